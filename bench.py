@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""Benchmark of the MFCC hot path (BASELINE.json: MFCC frames/s per B200).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step is one pass of the fused integer-mode kernel over the configs[1] workload of
+BASELINE.json: 10 000 synthetic 60 s int16 clips (960 000 samples each, 5645 frames per
+clip, 32 filters, 32 coefficients) per GPU.  `value` is frames/s with the clips
+resident in HBM; `e2e` is the same metric through MFCC.run_host() (the C-ABI call with
+host buffers): pinned host samples in, cepstra back in host memory, copies inside
+the timed region.  One process per GPU; no collective on the data path (clips are
+independent), NCCL only for the barriers and the max-over-ranks of the times.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_SAMPLES = 960000          # 60 s at 16 kHz
+N_CLIPS = 10000             # BASELINE.json configs[1]
+NFILT = NCEP = 32
+BYTES_PER_FRAME = 170 * 2 + NCEP * 2    # 340 B read + 64 B written
+SEED0 = 20260000
+
+
+def synth_clips(n_clips, n_samples, device, first_clip=0, out=None):
+    """The synthetic mixture of SURVEY.md 8(d) C2, by global clip index i:
+    i%4 == 0 uniform full-scale noise (drives the 16-bit mel wrap), 1 Gaussian
+    sigma 2000, 2 three sinusoids of amplitude 8000 + Gaussian sigma 50, 3 Gaussian
+    sigma 2000 gated in 0.5 s blocks (silence -> log2(0)).  Seeded per clip."""
+    import torch
+    if out is None:
+        out = torch.empty((n_clips, n_samples), dtype=torch.int16, device=device)
+    g = torch.Generator(device=device)
+    t = torch.arange(n_samples, device=device, dtype=torch.float32)
+    for j in range(n_clips):
+        i = first_clip + j
+        g.manual_seed(SEED0 + i)
+        c = i % 4
+        if c == 0:
+            out[j] = torch.randint(-32768, 32768, (n_samples,), generator=g, device=device,
+                                   dtype=torch.int32).to(torch.int16)
+            continue
+        if c == 2:
+            f = torch.rand(3, generator=g, device=device) * 7900.0 + 50.0
+            ph = torch.rand(3, generator=g, device=device) * 6.2831853
+            v = 8000.0 * torch.sin(t[None, :] * (6.2831853 / 16000.0) * f[:, None] + ph[:, None]).sum(0)
+            v = v + 50.0 * torch.randn(n_samples, generator=g, device=device)
+        else:
+            v = 2000.0 * torch.randn(n_samples, generator=g, device=device)
+            if c == 3:
+                v = v * ((torch.arange(n_samples, device=device) // 8000) % 2).to(torch.float32)
+        out[j] = v.clamp_(-32768, 32767).to(torch.int16)
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            p = [s.strip() for s in r.split(",")]
+            if len(p) < 8:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx = float(p[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), p[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_oracle_rate(n_clips, threads, repeats=1):
+    """Frames/s of the C oracle (oracle/mfcc_ref.c, the CPU restatement of the RTL) on
+    `n_clips` clips of the same workload.  This is the only place bench.py runs oracle/."""
+    import numpy as np
+    import torch
+    from oracle import ref_c as RC
+    cfg = RC.RefConfig(nfilters=NFILT, nceptrums=NCEP)
+    x = synth_clips(n_clips, N_SAMPLES, torch.device("cpu")).numpy()
+    frames = n_clips * cfg.num_frames(N_SAMPLES)
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        RC.run(cfg, x, threads=threads)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return frames / best, frames, best
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's integer pipeline on the host cores.  The
+    reference hot path is nMigen RTL and cannot run here (no nmigen, no simulator), so
+    this arm times the CPU restatement of it (oracle/mfcc_ref.c, "port") with all host
+    threads, on a bounded sample of the same workload per step."""
+    if rank != 0:
+        return
+    from oracle import ref_c as RC
+    import numpy as np
+    import torch
+    threads = RC.max_threads()
+    n_clips = max(threads, 8)
+    cfg = RC.RefConfig(nfilters=NFILT, nceptrums=NCEP)
+    x = synth_clips(n_clips, N_SAMPLES, torch.device("cpu")).numpy()
+    frames = n_clips * cfg.num_frames(N_SAMPLES)
+    for _ in range(args.warmup):
+        RC.run(cfg, x[: max(1, n_clips // 8)], threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        RC.run(cfg, x, threads=threads)
+    dt = (time.perf_counter() - t0) / args.steps
+    v = frames / dt
+    sample = "%d clips x 60 s (%d frames) per step" % (n_clips, frames)
+    print(json.dumps({
+        "impl": "reference", "metric": "mfcc_frames_per_sec", "value": v, "unit": "frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16",
+        "data": "synthetic", "audio_sec_per_sec": v * 170 / 16000,
+        "config": {"workload": "C2: synthetic 60 s int16 clips, 512/170 frames, 32 mel, 32 cepstra, "
+                               "integer mode (bounded sample)", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--clips", type=int, default=N_CLIPS, help="clips per GPU (default: configs[1])")
+    ap.add_argument("--e2e-clips", type=int, default=2048)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    import mfcc_b200
+    from mfcc_b200 import _lib
+    if args.warmup < 3:
+        args.warmup = 3
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    op = mfcc_b200.MFCC(nfilters=NFILT, nceptrums=NCEP, device=dev)
+    K = op.num_frames(N_SAMPLES)
+    x = torch.empty((args.clips, N_SAMPLES), dtype=torch.int16, device=dev)
+    synth_clips(args.clips, N_SAMPLES, dev, first_clip=rank * args.clips, out=x)
+    out = torch.empty((args.clips, K, NCEP), dtype=torch.int16, device=dev)
+    frames_rank = args.clips * K
+
+    for _ in range(args.warmup):
+        op(x, out=out)
+    barrier()
+    sampler = ClockSampler(local).start()
+    l0 = _lib.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record()
+    for s in range(args.steps):
+        op(x, out=out)          # one kernel launch on torch's current stream
+        ev[s + 1].record()
+    barrier()
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop()
+    t_total = ev[0].elapsed_time(ev[-1]) * 1e-3
+    kern = sorted(ev[i].elapsed_time(ev[i + 1]) * 1e-3 for i in range(args.steps))
+    t_kernel_avg = sum(kern) / len(kern)
+    tt = torch.tensor([t_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_max = float(tt.item())
+    value = frames_rank * world * args.steps / t_max
+
+    # ---- end to end: pinned host buffers through the C-ABI host entry point
+    ne = min(args.e2e_clips, args.clips)
+    xh = torch.empty((ne, N_SAMPLES), dtype=torch.int16).pin_memory()
+    xh.copy_(x[:ne])
+    oh = torch.empty((ne, K, NCEP), dtype=torch.int16).pin_memory()
+    e_steps = max(1, min(args.steps, 5))
+    op.run_host(xh, out=oh)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e_steps):
+        op.run_host(xh, out=oh)
+    torch.cuda.synchronize()
+    te = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = ne * K * world * e_steps / float(te.item())
+    e2e_ok = bool(torch.equal(oh.to(dev), out[:ne]))
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = frames_rank * BYTES_PER_FRAME / t_kernel_avg / 1e9
+        line = {
+            "metric": "mfcc_frames_per_sec", "value": value, "unit": "frames/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_max / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16",
+            "data": "synthetic", "audio_sec_per_sec": value * 170 / 16000,
+            "config": {"workload": "C2: %d synthetic 60 s int16 clips per GPU (960000 samples, 5645 "
+                                   "frames each), 512/170 frames, 32 mel, 32 cepstra, integer "
+                                   "(bit-exact) mode" % args.clips,
+                       "clips_per_gpu": args.clips, "frames_per_step_per_gpu": frames_rank,
+                       "l2": "inputs (%.1f GB per step) larger than L2, no flush needed"
+                             % (args.clips * N_SAMPLES * 2 / 1e9),
+                       "e2e_clips": ne, "e2e_steps": e_steps, "e2e_matches_device_path": e2e_ok},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None,
+                         "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
+                         "kernel": "mfcc_int_fused<32>", "kernel_ms": t_kernel_avg * 1e3,
+                         "bytes_per_frame": BYTES_PER_FRAME,
+                         "note": "integer-issue bound, not HBM bound: see DESIGN.md"},
+            "e2e": {"value": e2e_value, "unit": "frames/s",
+                    "h2d_bytes_per_step": ne * N_SAMPLES * 2, "d2h_bytes_per_step": ne * K * NCEP * 2},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import ref_c as RC
+            thr = RC.max_threads()
+            ncl = max(thr, 8)
+            v, fr, dt = cpu_oracle_rate(ncl, thr)
+            line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": thr, "kind": "port",
+                                    "sample": "%d clips x 60 s (%d frames), %.1f s" % (ncl, fr, dt)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

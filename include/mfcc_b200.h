@@ -1,0 +1,159 @@
+/*
+ * mfcc_b200.h -- C ABI of the B200 MFCC path (libmfcc_b200.so).
+ *
+ * The reference (lambdaconcept/mfcc) has no FFI layer: its hot path is an nMigen
+ * hardware pipeline whose interface is a chain of stream endpoints
+ * (/root/reference/mfcc/core/mfcc.py:19-30, :90-104) and whose host side talks to
+ * the FPGA over USB (software/main.c:100-177).  The entry points below are what a
+ * host binding for this path replaces those with; each one cites the reference
+ * interface it stands in for.  INTEGRATION.md shows the binding stubs.
+ *
+ * Conventions (same as the reference's C tools, software/ft601.h:43-50,
+ * software/cepstrum.h:20-24): plain pointers and sizes, caller owns every buffer,
+ * 0 on success and a negative code on failure, never aborts.
+ * Pointers named d_* are DEVICE pointers; h_* are HOST pointers.
+ * `stream` is a cudaStream_t passed as void* (NULL = default stream); every device
+ * entry point is asynchronous on it.  A handle is not thread-safe; handles are
+ * independent.
+ */
+#ifndef MFCC_B200_H
+#define MFCC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MFCC_B200_OK            0
+#define MFCC_B200_EINVAL      (-1)   /* bad argument */
+#define MFCC_B200_EUNSUPPORTED (-2)  /* configuration the kernels do not cover */
+#define MFCC_B200_ECUDA       (-3)   /* CUDA runtime error, see mfcc_b200_last_error() */
+
+#define MFCC_B200_MODE_INT   0   /* bit-exact fixed point (the FPGA's arithmetic) */
+#define MFCC_B200_MODE_FP32  1   /* float32, notebook/MFCC-INT.ipynb structure */
+
+/* Stage identifiers, in pipeline order (mfcc/core/mfcc.py:90-104). */
+enum mfcc_b200_stage_id {
+    MFCC_B200_STAGE_PREEMPH = 0,  /* Preemph         mfcc/core/preemph.py:9-30      int16[n]        -> int16[n]          */
+    MFCC_B200_STAGE_FRAME   = 1,  /* Frame           mfcc/core/frame.py:49-155      int16[n]        -> int16[K][nfft]    */
+    MFCC_B200_STAGE_WINDOW  = 2,  /* WindowHamming   mfcc/core/window.py:10-126     int16[K][nfft]  -> int16[K][nfft]    */
+    MFCC_B200_STAGE_FFT     = 3,  /* FftStream       mfcc/core/fft_stream.py:6-73   int16[K][nfft]  -> int16[K][nfft/2][2] (re,im) */
+    MFCC_B200_STAGE_POWER   = 4,  /* PowerSpectrum   mfcc/core/pow2.py:43-70        int16[K][nfft/2][2] -> uint32[K][nfft/2] */
+    MFCC_B200_STAGE_MEL     = 5,  /* FilterBank      mfcc/core/filterbank.py:37-144 uint32[K][nfft/2] -> uint16[K][nfilters] */
+    MFCC_B200_STAGE_LOG2    = 6,  /* Log2Fix         mfcc/core/log.py:107-139       uint16[K][nfilters] -> uint16[K][nfilters] */
+    MFCC_B200_STAGE_DCT     = 7,  /* DCTStream       mfcc/core/dct_stream.py:6-73   uint16[K][nfilters] -> int16[K][nfilters] */
+    MFCC_B200_STAGE_COUNT   = 8   /* Discard (mfcc/misc/discard.py) is a slice; the host does it */
+};
+
+/*
+ * Configuration = the arguments of MFCC(width, nfft, samplerate, nfilters, nceptrums)
+ * (mfcc/core/mfcc.py:19-26), the constants MFCC.elaborate hands to its stages
+ * (:38-88) and the ROM contents those stages compute when the design is elaborated
+ * (window.py:22-43, fft.py:28-36, filterbank.py:15-34).  The tables are HOST arrays,
+ * copied by mfcc_b200_create(); mfcc_b200/tables.py builds them.
+ */
+typedef struct mfcc_b200_cfg {
+    int32_t struct_size;     /* sizeof(mfcc_b200_cfg), for ABI checking */
+    int32_t mode;            /* MFCC_B200_MODE_* */
+    int32_t nfft;            /* 512 (the only size the kernels cover) */
+    int32_t hop;             /* nfft/3 = 170            mfcc/core/mfcc.py:43 */
+    int32_t nfilters;        /* 16 or 32                mfcc/core/mfcc.py:21 */
+    int32_t nceptrums;       /* 1..nfilters             mfcc/core/mfcc.py:21 */
+    int32_t window_shift;    /* precision+1 = 9         mfcc/core/window.py:20, :84 */
+    int32_t pow_shift;       /* 32-width_output = 2     mfcc/core/pow2.py:64 */
+    int32_t mel_wbits;       /* 30                      mfcc/core/filterbank.py:49-52 */
+    int32_t mel_lo_bit;      /* first kept bit of the mel accumulator: 31 (32 filters),
+                                32 (16 filters)         mfcc/core/filterbank.py:71, :122 */
+    int32_t mel_out_bits;    /* 16                      mfcc/core/mfcc.py:70 */
+    int32_t log_precision;   /* 11                      mfcc/core/log.py:114 */
+    int32_t log_out_bits;    /* 15                      mfcc/core/mfcc.py:82 */
+    int32_t reserved[3];
+    const int32_t  *window_curve;  /* [nfft]            multiplier per sample position */
+    const int32_t  *tw_fft;        /* [nfft/2][2]       decoded twiddle ROM (re, im) of the nfft-point FFT */
+    const int32_t  *tw_dct;        /* [2*nfilters][2]   decoded twiddle ROM of the 4*nfilters-point FFT */
+    const uint32_t *mel_weight;    /* [nfft/2]          weight applied to each bin */
+    const uint8_t  *mel_close;     /* [nfft/2]          1 where a bin closes its segment */
+    /* fp32 mode only (may be NULL in int mode) */
+    const float    *f_window;      /* [nfft]                   */
+    const float    *f_mel;         /* [nfilters][nfft/2+1]     */
+    const float    *f_dct;         /* [nfilters][nfilters]     */
+    float           f_preemph;     /* 0.96875                  */
+    float           f_mel_floor;   /* mel energies are clamped to this before log2 (0 = off) */
+} mfcc_b200_cfg;
+
+/* Per-stage outputs of one clip (device pointers, any may be NULL).
+ * The analogue of the collector processes of the reference's simulation bench,
+ * mfcc/core/mfcc.py:176-183. */
+typedef struct mfcc_b200_taps {
+    int16_t  *d_window;   /* [K][nfft]        */
+    int16_t  *d_fft;      /* [K][nfft/2][2]   */
+    uint32_t *d_power;    /* [K][nfft/2]      */
+    uint16_t *d_mel;      /* [K][nfilters]    */
+    uint16_t *d_log2;     /* [K][nfilters]    */
+    int16_t  *d_dct;      /* [K][nfilters]    */
+} mfcc_b200_taps;
+
+/* Replaces elaborating MFCC(...) (mfcc/core/mfcc.py:32-117) and loading the
+ * bitstream: uploads the ROM tables to the current CUDA device. */
+int  mfcc_b200_create(const mfcc_b200_cfg *cfg, void **handle);
+void mfcc_b200_destroy(void *handle);
+
+/*
+ * Whole chain, fused, cepstra only.  Replaces the loop of mfcc_convert()
+ * (software/main.c:128-166: write nfft then hop samples, read nceptrums words per
+ * round) and the data path MFCC.sink -> MFCC.source (mfcc/core/mfcc.py:90-104).
+ *   d_x      n_clips rows of n_samples int16, row pitch clip_stride (samples);
+ *            every row is an independent stream that starts from reset
+ *   n_frames frames to produce per clip.  Frame k covers samples hop*k .. hop*k+nfft-1;
+ *            samples at or beyond n_samples read as zero, which is what the reference
+ *            hosts feed after the end of the audio (software/main.c:135-144)
+ *   d_out    n_clips rows of n_frames*nceptrums int16 (int mode) or float (fp32 mode),
+ *            row pitch out_clip_stride (elements)
+ *   taps     optional, requires n_clips == 1
+ */
+int  mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t n_samples,
+                   int32_t n_clips, int64_t n_frames, void *d_out, int64_t out_clip_stride,
+                   const mfcc_b200_taps *taps, void *stream);
+
+/*
+ * Same call with HOST buffers: the library stages the clips through pinned memory
+ * and overlaps host->device copy, kernel and device->host copy in chunks of clips.
+ * This is the entry point a host tool in the place of software/main.c binds.
+ * Synchronous: returns when h_out is complete.
+ */
+int  mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, int64_t n_samples,
+                        int32_t n_clips, int64_t n_frames, void *h_out, int64_t out_clip_stride);
+
+/*
+ * One stage on its own (device buffers), the analogue of instantiating a single
+ * stage module (constructors listed in the enum above).  n is the number of input
+ * samples for PREEMPH and FRAME and the number of frames K otherwise; for FRAME
+ * n_frames rows are produced (zero-extended like mfcc_b200_run).  `prev` is the
+ * sample before d_in[0] for PREEMPH (0 after reset, preemph.py:18).
+ */
+int  mfcc_b200_stage(void *handle, int32_t stage, const void *d_in, void *d_out, int64_t n,
+                     int64_t n_frames, int32_t prev, void *stream);
+
+/*
+ * Streaming: one hop per stream per call, the mic2mfcc use of the core
+ * (mfcc/targets/mic2mfcc.py:19-30).  d_state holds, per stream, the last nfft-hop
+ * raw samples and the sample before them (what Preemph.odata and the Frame ring
+ * hold, preemph.py:18-21, frame.py:65-73).  Zero state = the core after reset with
+ * nfft-hop zeros already pushed in.
+ *   d_hop  [n_streams][hop] int16     d_out [n_streams][nceptrums]
+ */
+int  mfcc_b200_state_bytes(void *handle, int32_t n_streams, int64_t *bytes);
+int  mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n_streams,
+                    void *d_out, void *stream);
+
+/* Number of kernels this library has launched since it was loaded (bench.py's
+ * gpu_launches). */
+int64_t     mfcc_b200_launch_count(void);
+const char *mfcc_b200_last_error(void);
+int         mfcc_b200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MFCC_B200_H */

@@ -1,0 +1,281 @@
+// Device-side building blocks of the B200 MFCC path (integer mode).
+//
+// One warp computes one frame.  The 512-point FFT runs as 4 + 4 + 1 radix-2 stages:
+// stages 0-3 and 4-7 entirely in registers (16 complex values per lane) with two
+// shared-memory exchanges in between, stage 8 fused with the power spectrum.
+// Every radix-2 stage keeps the reference's rounding: the butterfly below yields,
+// bit for bit, Butterfly(width=16, bias_width=14, scale_bit=1) of
+// /root/reference/mfcc/misc/fft.py:64-194.
+//
+// tests/lane_model.py mirrors this file step by step in numpy.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mfccb {
+
+constexpr int NFFT   = 512;
+constexpr int HOP    = 170;      // nfft // 3, mfcc/core/mfcc.py:43
+constexpr int NBINS  = 256;      // FftStream emits bins 0..255, fft_stream.py:24,28
+constexpr int XW     = 656;      // 32-bit words of the per-warp exchange buffer
+constexpr unsigned FULL = 0xffffffffu;
+
+// Tables every CTA copies from global to shared memory once (16-byte multiples).
+struct alignas(16) DevTables {
+    int2     twB[128];       // stages 4..7, doubled (2re, 2im): [16 | 16 | 32 | 64] entries
+    int2     tw8[256];       // stage 8, doubled, natural order
+    uint32_t melw[256];      // weight per bin, filterbank.py:90-115
+    int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
+    int2     dct_twf[32];    // final DCT stage, lane j = bin j, doubled
+    int16_t  curve[512];     // window multipliers, window.py:59-115
+    int16_t  seg_first[40];  // first bin of mel segment g
+    int16_t  seg_close[40];  // closing bin of mel segment g
+    int32_t  mel_lo_bit;     // filterbank.py:122
+    int32_t  nseg;
+    int32_t  pad[2];
+};
+static_assert(sizeof(DevTables) % 16 == 0, "DevTables must be int4-copyable");
+
+// W512^(32k), k = 0..7: the only twiddles stages 0..3 need (fft.py:28-36, :43-59).
+// mfcc_b200_create() checks them against the ROM the host passes in.
+__device__ constexpr int TWA_RE[8] = {16384, 15137, 11585, 6270, 0, -6270, -11585, -15137};
+__device__ constexpr int TWA_IM[8] = {0, -6270, -11585, -15137, -16384, -15137, -11585, -6270};
+constexpr int H_TWA_RE[8] = {16384, 15137, 11585, 6270, 0, -6270, -11585, -15137};
+constexpr int H_TWA_IM[8] = {0, -6270, -11585, -15137, -16384, -15137, -11585, -6270};
+
+__host__ __device__ constexpr int brev4(int v) {
+    return ((v & 1) << 3) | ((v & 2) << 1) | ((v & 4) >> 1) | ((v & 8) >> 3);
+}
+
+// ---------------------------------------------------------------------------------
+// Butterfly.  With P = x1*w (complex, 30-bit products) the RTL computes
+//   t  = (P + 8191) >> 14
+//   y0 = wrap16((x0 + t) >> 1),  y1 = wrap16((x0 - t) >> 1)        fft.py:93-96, :188-191
+// (x0 + t) >> 1 = ((x0 << 14) + P + 8191) >> 15, so y0 is bits 15..30 of that sum.
+// Doubling everything puts those bits in the top half of a 32-bit register:
+//   s0 = (x0 << 15) + 2P + 16382,   y0 = s0 >> 16 (arithmetic)
+// and the natural 32-bit wrap of s0 *is* the 16-bit wrap of the hardware.  Likewise
+//   x0 - t = ((x0 << 14) - P + 8192) >> 14   (floor of a negated floor)
+//   s1 = (x0 << 15) - 2P + 16384 = (x0 << 15) - q + 32766 with q = 2P + 16382.
+// w2r, w2i are the doubled twiddle components.
+struct Bf { unsigned s0r, s0i, s1r, s1i; };
+
+__device__ __forceinline__ Bf bf_core(int x0r, int x0i, int x1r, int x1i, int w2r, int w2i) {
+    unsigned qr = (unsigned)(x1r * w2r) - (unsigned)(x1i * w2i) + 16382u;
+    unsigned qi = (unsigned)(x1i * w2r) + (unsigned)(x1r * w2i) + 16382u;
+    unsigned br = (unsigned)x0r << 15;
+    unsigned bi = (unsigned)x0i << 15;
+    Bf o;
+    o.s0r = br + qr;
+    o.s0i = bi + qi;
+    o.s1r = br - qr + 32766u;
+    o.s1i = bi - qi + 32766u;
+    return o;
+}
+
+// in-place, unpacked (sign-extended 16-bit values in 32-bit registers)
+__device__ __forceinline__ void bf(int &x0r, int &x0i, int &x1r, int &x1i, int w2r, int w2i) {
+    Bf o = bf_core(x0r, x0i, x1r, x1i, w2r, w2i);
+    x0r = (int)o.s0r >> 16; x0i = (int)o.s0i >> 16;
+    x1r = (int)o.s1r >> 16; x1i = (int)o.s1i >> 16;
+}
+
+// packed outputs (re in the low half, im in the high half): one PRMT per value
+__device__ __forceinline__ void bf_pk(int x0r, int x0i, int x1r, int x1i, int w2r, int w2i,
+                                      unsigned &p0, unsigned &p1) {
+    Bf o = bf_core(x0r, x0i, x1r, x1i, w2r, w2i);
+    p0 = __byte_perm(o.s0r, o.s0i, 0x7632);
+    p1 = __byte_perm(o.s1r, o.s1i, 0x7632);
+}
+
+__device__ __forceinline__ int lo16(unsigned w) { return (int)(short)(w & 0xffffu); }
+__device__ __forceinline__ int hi16(unsigned w) { return (int)w >> 16; }
+
+// exchange 1: pass-A lane `row` owns positions 16*row + col.  The skew makes both
+// the 128-bit row stores and the column reads of pass B conflict free.
+__device__ __forceinline__ int xa_addr(int row, int col) { return row * 20 + col + ((row >> 4) << 4); }
+
+// ---------------------------------------------------------------------------------
+// FFT-512 of one frame by one warp.
+//   xr[l]  in: windowed sample for position 16*lane + l, i.e. sample index
+//              brev5(lane) + 32*brev4(l)   (bit-reversed load, fft.py:413-418)
+//   out: re[i], im[i] = bin lane + 32*i, i = 0..7
+__device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const DevTables *tab,
+                                            int lane, int (&re)[8], int (&im)[8])
+{
+    int xi[16];
+#pragma unroll
+    for (int l = 0; l < 16; ++l) xi[l] = 0;                  // fft_stream.py:33
+
+    // ---- stages 0..2 in registers; twiddle index k*(256>>s) = 32*(k*(8>>s))
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int half = 1 << s;
+#pragma unroll
+        for (int l = 0; l < 16; ++l) {
+            if (l & half) continue;
+            const int t = (l & (half - 1)) * (8 >> s);
+            bf(xr[l], xi[l], xr[l + half], xi[l + half], 2 * TWA_RE[t], 2 * TWA_IM[t]);
+        }
+    }
+    // ---- stage 3, packed straight into the exchange buffer
+    {
+        unsigned pk[16];
+#pragma unroll
+        for (int l = 0; l < 8; ++l)
+            bf_pk(xr[l], xi[l], xr[l + 8], xi[l + 8], 2 * TWA_RE[l], 2 * TWA_IM[l], pk[l], pk[l + 8]);
+        uint4 *row = reinterpret_cast<uint4 *>(xbuf + xa_addr(lane, 0));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) row[q] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+    }
+    __syncwarp();
+    // ---- pass B: lane (h, l4) takes positions 256h + 16m + l4, m = 0..15
+    const int h = lane >> 4, l4 = lane & 15;
+#pragma unroll
+    for (int m = 0; m < 16; ++m) {
+        unsigned w = xbuf[xa_addr(16 * h + m, l4)];
+        xr[m] = lo16(w); xi[m] = hi16(w);
+    }
+    __syncwarp();
+    // stage s pairs m, m + 2^(s-4); twiddle index ((m mod 2^(s-4))*16 + l4) * (256 >> s).
+    // Indices >= 128 are the stored entry turned by -j: (re, im) -> (im, -re)  (fft.py:55-59)
+    {   // stage 4: one twiddle per lane
+        const int2 w = tab->twB[l4];
+#pragma unroll
+        for (int m = 0; m < 16; m += 2) bf(xr[m], xi[m], xr[m + 1], xi[m + 1], w.x, w.y);
+    }
+    {   // stage 5
+        const int2 w = tab->twB[16 + l4];
+#pragma unroll
+        for (int m = 0; m < 16; m += 4) {
+            bf(xr[m], xi[m], xr[m + 2], xi[m + 2], w.x, w.y);
+            bf(xr[m + 1], xi[m + 1], xr[m + 3], xi[m + 3], w.y, -w.x);
+        }
+    }
+    {   // stage 6
+#pragma unroll
+        for (int mm = 0; mm < 2; ++mm) {
+            const int2 w = tab->twB[32 + mm * 16 + l4];
+#pragma unroll
+            for (int m = 0; m < 16; m += 8) {
+                bf(xr[m + mm], xi[m + mm], xr[m + mm + 4], xi[m + mm + 4], w.x, w.y);
+                bf(xr[m + mm + 2], xi[m + mm + 2], xr[m + mm + 6], xi[m + mm + 6], w.y, -w.x);
+            }
+        }
+    }
+    {   // stage 7, packed into the exchange buffer at natural position + 16*(p >> 8)
+        unsigned *dst = xbuf + 272 * h + l4;
+#pragma unroll
+        for (int mm = 0; mm < 4; ++mm) {
+            const int2 w = tab->twB[64 + mm * 16 + l4];
+            unsigned a0, a1, b0, b1;
+            bf_pk(xr[mm], xi[mm], xr[mm + 8], xi[mm + 8], w.x, w.y, a0, a1);
+            bf_pk(xr[mm + 4], xi[mm + 4], xr[mm + 12], xi[mm + 12], w.y, -w.x, b0, b1);
+            dst[16 * mm] = a0;        dst[16 * (mm + 8)] = a1;
+            dst[16 * (mm + 4)] = b0;  dst[16 * (mm + 12)] = b1;
+        }
+    }
+    __syncwarp();
+    // ---- stage 8: only y0 is ever read (bins 0..255, fft_stream.py:24)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int b = lane + 32 * i;
+        const unsigned u0 = xbuf[b], u1 = xbuf[272 + b];
+        const int2 w = tab->tw8[b];
+        const int x1r = lo16(u1), x1i = hi16(u1);
+        unsigned qr = (unsigned)(x1r * w.x) - (unsigned)(x1i * w.y) + 16382u;
+        unsigned qi = (unsigned)(x1i * w.x) + (unsigned)(x1r * w.y) + 16382u;
+        re[i] = (int)(((unsigned)lo16(u0) << 15) + qr) >> 16;
+        im[i] = (int)(((unsigned)hi16(u0) << 15) + qi) >> 16;
+    }
+    __syncwarp();   // xbuf may be reused by the caller
+}
+
+// ---------------------------------------------------------------------------------
+// FilterBank.  pw[0..255] in shared memory.  Returns the 16-bit mel value of filter
+// (lane mod NF).  Segment g = bins seg_first[g] .. seg_close[g]; with
+//   A_g = sum d*w over the non-closing bins, D_g = sum d, PK_g = d at the closing bin
+// the register the hardware reads at the close of segment g is
+//   A_{g-1} + (PK_{g-1} << 30) + (D_g << 30) - A_g         filterbank.py:119-142
+// of which bits lo_bit .. lo_bit+15 are kept (:122): arithmetic modulo 2^64 is exact.
+template <int NF>
+__device__ __forceinline__ unsigned mel_warp(const unsigned *pw, const DevTables *tab, int lane)
+{
+    // segment 0 (output suppressed, filterbank.py:139) is cheap; every lane does it
+    unsigned long long a0 = 0;
+    const int c0 = tab->seg_close[0];
+    for (int b = tab->seg_first[0]; b < c0; ++b) a0 += (unsigned long long)pw[b] * tab->melw[b];
+    const unsigned pk0 = pw[c0];
+
+    const int g = (lane & (NF - 1)) + 1;
+    const int first = tab->seg_first[g], cl = tab->seg_close[g];
+    unsigned long long a = 0;
+    unsigned d = 0;
+    for (int b = first; b < cl; ++b) {
+        const unsigned v = pw[b];
+        a += (unsigned long long)v * tab->melw[b];
+        d += v;
+    }
+    const unsigned pk = pw[cl];
+    unsigned long long pa = __shfl_up_sync(FULL, a, 1);
+    unsigned ppk = __shfl_up_sync(FULL, pk, 1);
+    if ((lane & (NF - 1)) == 0) { pa = a0; ppk = pk0; }
+    const unsigned e = ppk + d;
+    const unsigned long long x = pa - a + ((unsigned long long)e << 30);
+    return (unsigned)(x >> tab->mel_lo_bit) & 0xffffu;
+}
+
+// Log2Fix(16, 15) -> Log2FixCalc(27, 11), log.py:123-126, :57-62, :80-102, :133.
+// The SHIFT-RIGHT loop runs floor(log2 m) times; the ten squarings set fraction
+// bits 10..1 (bit 0 is never reached: cnt stops at 1).
+__device__ __forceinline__ unsigned log2fix_lane(unsigned m)
+{
+    const unsigned mm = m ? m : 1u;
+    const int sh = 31 - __clz(mm);
+    unsigned z = (mm << 11) >> sh;
+    unsigned frac = 0;
+#pragma unroll
+    for (int it = 0; it < 10; ++it) {
+        const unsigned c = z * z;
+        const unsigned bit = (c >> 23) & 1u;
+        z = c >> (11 + bit);
+        frac = (frac << 1) | bit;
+    }
+    return (((unsigned)sh << 11) + (frac << 1)) & 0x7fffu;
+}
+
+// DCTStream(nfft=NF): a 4NF-point FFT of [0,a,0,b,...,0,b,0,a], real part of bins
+// 0..NF-1 (dct_stream.py:29-37).  The even-index half of the first DIT split is all
+// zero and yields exact zeros, so only the 2NF-point sub-FFT of the odd samples
+// u[m] = L[m], u[2NF-1-m] = L[m] is computed: stage 0 inside the lane, stages
+// 1..S-1 by exchanging one value with lane ^ 2^(s-1), then the last stage of the
+// 4NF FFT with x0 = 0.  Lane j ends up owning bin j (tests/lane_model.py: dct_plan).
+template <int NF>
+__device__ __forceinline__ int dct_warp(unsigned L, const DevTables *tab, int lane)
+{
+    constexpr int S  = (NF == 32) ? 6 : 5;
+    constexpr int NB = (NF == 32) ? 5 : 4;
+    const int j = lane & (NF - 1);
+    const int src = (int)(__brev((unsigned)j) >> (32 - NB));
+    const int base = lane & ~(NF - 1);
+    int a = (int)__shfl_sync(FULL, L, base + src);
+    int b = (int)__shfl_sync(FULL, L, base + NF - 1 - src);
+    // stage 0: real inputs < 2^15, twiddle 1: no wrap can occur
+    unsigned p0 = (unsigned)((a + b) >> 1) & 0xffffu;       // im = 0
+    unsigned p1 = (unsigned)((a - b) >> 1) & 0xffffu;
+#pragma unroll
+    for (int s = 1; s < S; ++s) {
+        const bool up = (lane >> (s - 1)) & 1;
+        const unsigned send = up ? p0 : p1;
+        const unsigned rc = __shfl_xor_sync(FULL, send, 1 << (s - 1));
+        const unsigned x0 = up ? rc : p0;
+        const unsigned x1 = up ? p1 : rc;
+        const int2 w = tab->dct_tw[s * 32 + j];
+        bf_pk(lo16(x0), hi16(x0), lo16(x1), hi16(x1), w.x, w.y, p0, p1);
+    }
+    const int2 w = tab->dct_twf[j];
+    const unsigned q = (unsigned)(lo16(p0) * w.x) - (unsigned)(hi16(p0) * w.y) + 16382u;
+    return (int)q >> 16;
+}
+
+}  // namespace mfccb

@@ -1,0 +1,708 @@
+// Kernels and C ABI of the B200 MFCC path (include/mfcc_b200.h).
+//
+// mfcc_int_fused: the whole chain Preemph -> Frame -> WindowHamming -> FftStream ->
+// PowerSpectrum -> FilterBank -> Log2Fix -> DCTStream -> Discard of
+// /root/reference/mfcc/core/mfcc.py:90-104 in one launch.  A CTA of 8 warps walks
+// tiles of 32 consecutive frames of one clip: the tile's int16 sample run arrives in
+// shared memory through one TMA bulk copy (prefetched while the previous tile is
+// computed), is pre-emphasised once, and each warp then turns frames into cepstra;
+// only the cepstra go back to HBM.
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <cuda_runtime.h>
+#include <atomic>
+#include <string>
+#include <vector>
+
+#include "../../include/mfcc_b200.h"
+#include "mfcc_dev.cuh"
+
+using namespace mfccb;
+
+namespace {
+
+constexpr int WARPS   = 8;
+constexpr int THREADS = WARPS * 32;
+constexpr int FT      = 32;                                        // frames per tile
+constexpr int RAWN    = ((HOP * (FT - 1) + NFFT + 15) + 7) & ~7;   // samples per tile buffer
+constexpr int CTAS_PER_SM = 4;
+
+struct RunParams {
+    const int16_t *x;
+    long long clip_stride, n_samples, n_frames;
+    int16_t *out;
+    long long out_clip_stride;
+    const DevTables *tab;
+    long long n_tiles;
+    int tiles_per_clip;
+    int nceptrums;
+    int aligned;          // rows are 16-byte aligned: TMA path
+    mfcc_b200_taps taps;  // all NULL unless requested (n_clips == 1)
+};
+
+// ------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MBAR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MBAR_DONE;\n"
+        "bra MBAR_WAIT;\n"
+        "MBAR_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// ------------------------------------------------------------------ tile geometry
+struct Tile {
+    const int16_t *clip;
+    long long ci, f0, a0;    // clip index, first frame, sample index of raw[0] (multiple of 8, may be -8)
+    int nf, len, lo, hi;     // frames, samples needed in raw[], TMA covers raw[lo, hi)
+};
+
+__device__ __forceinline__ Tile tile_geo(const RunParams &p, long long t) {
+    Tile g;
+    g.ci = t / p.tiles_per_clip;
+    g.f0 = (t - g.ci * p.tiles_per_clip) * FT;
+    long long left = p.n_frames - g.f0;
+    g.nf = left < FT ? (int)left : FT;
+    g.clip = p.x + g.ci * p.clip_stride;
+    g.a0 = ((HOP * g.f0) & ~7LL) - 8;                       // <= HOP*f0 - 1: the predecessor sample
+    g.len = (int)(HOP * (g.f0 + g.nf - 1) + NFFT - g.a0);   // <= RAWN
+    long long lo = g.a0 < 0 ? 0 : g.a0;
+    long long hi = g.a0 + ((g.len + 7) & ~7);
+    long long lim = p.n_samples & ~7LL;
+    if (hi > lim) hi = lim;
+    if (!p.aligned || hi < lo) hi = lo;
+    g.lo = (int)(lo - g.a0);
+    g.hi = (int)(hi - g.a0);
+    return g;
+}
+
+// ------------------------------------------------------------------ one frame by one warp
+// pre: pre-emphasised samples of the frame in shared memory (even halfword offset).
+template <int NF>
+__device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, const DevTables *tab, int lane,
+                                           int16_t *out, int nceptrums, const mfcc_b200_taps &tp, long long k)
+{
+    // WindowHamming: top 16 bits of signed16 * unsigned9 = (y * curve) >> 9   window.py:74-75,84
+    const int bt = (int)(__brev((unsigned)lane) >> 27);
+    int xr[16];
+#pragma unroll
+    for (int l = 0; l < 16; ++l) {
+        const int n = bt + 32 * brev4(l);
+        xr[l] = ((int)pre[n] * (int)tab->curve[n]) >> 9;
+        if (tp.d_window) tp.d_window[k * NFFT + n] = (int16_t)xr[l];
+    }
+    int re[8], im[8];
+    fft512_warp(xr, xbuf, tab, lane, re, im);
+    // PowerSpectrum: top 30 bits of the 32-bit sum   pow2.py:32, :64
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int b = lane + 32 * i;
+        const unsigned pw = ((unsigned)(re[i] * re[i]) + (unsigned)(im[i] * im[i])) >> 2;
+        xbuf[b] = pw;
+        if (tp.d_fft) { tp.d_fft[(k * NBINS + b) * 2] = (int16_t)re[i]; tp.d_fft[(k * NBINS + b) * 2 + 1] = (int16_t)im[i]; }
+        if (tp.d_power) tp.d_power[k * NBINS + b] = pw;
+    }
+    __syncwarp();
+    const unsigned mel = mel_warp<NF>(xbuf, tab, lane);
+    const unsigned lg = log2fix_lane(mel);
+    const int c = dct_warp<NF>(lg, tab, lane);
+    __syncwarp();   // xbuf is rewritten by the next frame
+    if (lane < NF) {
+        if (tp.d_mel)  tp.d_mel[k * NF + lane] = (uint16_t)mel;
+        if (tp.d_log2) tp.d_log2[k * NF + lane] = (uint16_t)lg;
+        if (tp.d_dct)  tp.d_dct[k * NF + lane] = (int16_t)c;
+    }
+    if (lane < nceptrums) out[lane] = (int16_t)c;            // Discard, discard.py:27-55
+}
+
+// ------------------------------------------------------------------ fused kernel
+struct Smem {
+    DevTables tab;
+    alignas(16) int16_t raw[RAWN];
+    alignas(16) int16_t pre[RAWN];
+    alignas(16) unsigned xbuf[WARPS][XW];
+    alignas(8) uint64_t mbar;
+};
+
+__device__ __forceinline__ void issue_tile(const RunParams &p, long long t, Smem *sm) {
+    const Tile g = tile_geo(p, t);
+    const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
+    if (bytes) {
+        mbar_arrive_expect_tx(&sm->mbar, bytes);
+        tma_load_1d(sm->raw + g.lo, g.clip + g.a0 + g.lo, bytes, &sm->mbar);
+    } else {
+        mbar_arrive(&sm->mbar);
+    }
+}
+
+template <int NF>
+__global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const RunParams p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem *sm = reinterpret_cast<Smem *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    {   // tables: global -> shared, once per CTA
+        const int4 *src = reinterpret_cast<const int4 *>(p.tab);
+        int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
+        for (int i = tid; i < (int)(sizeof(DevTables) / 16); i += THREADS) dst[i] = src[i];
+    }
+    if (tid == 0) mbar_init(&sm->mbar, 1);
+    __syncthreads();
+
+    long long tile = blockIdx.x;
+    if (tid == 0 && tile < p.n_tiles) issue_tile(p, tile, sm);
+    uint32_t phase = 0;
+
+    for (; tile < p.n_tiles; tile += gridDim.x) {
+        const Tile g = tile_geo(p, tile);
+        // samples the bulk copy does not cover: before the clip (zeros), the ragged
+        // tail and everything past the end (zeros, software/main.c:135-144)
+        for (int j = tid; j < g.lo; j += THREADS) sm->raw[j] = 0;
+        for (int j = g.hi + tid; j < g.len; j += THREADS) {
+            const long long s = g.a0 + j;
+            sm->raw[j] = (s >= 0 && s < p.n_samples) ? g.clip[s] : (int16_t)0;
+        }
+        mbar_wait(&sm->mbar, phase);
+        phase ^= 1;
+        __syncthreads();
+
+        // Preemph, once per sample: y = x + (prev >> 5) - prev, 16-bit   preemph.py:18-28
+        {
+            const unsigned *r32 = reinterpret_cast<const unsigned *>(sm->raw);
+            unsigned *p32 = reinterpret_cast<unsigned *>(sm->pre);
+            const int nw = (g.len + 1) >> 1;
+            for (int i = tid; i < nw; i += THREADS) {
+                const unsigned w1 = r32[i];
+                const int sp = i ? hi16(r32[i - 1]) : 0;
+                const int s0 = lo16(w1), s1 = hi16(w1);
+                const int y0 = s0 + (sp >> 5) - sp;
+                const int y1 = s1 + (s0 >> 5) - s0;
+                p32[i] = __byte_perm((unsigned)y0, (unsigned)y1, 0x5410);
+            }
+        }
+        __syncthreads();
+        {   // raw[] is free again: prefetch the next tile while this one is computed
+            const long long nxt = tile + gridDim.x;
+            if (tid == 0 && nxt < p.n_tiles) issue_tile(p, nxt, sm);
+        }
+        const int off0 = (int)(HOP * g.f0 - g.a0);          // even, 8..14
+        int16_t *orow = p.out + g.ci * p.out_clip_stride;
+        for (int fl = warp; fl < g.nf; fl += WARPS) {
+            const long long k = g.f0 + fl;
+            frame_warp<NF>(sm->pre + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
+                           orow + k * p.nceptrums, p.nceptrums, p.taps, k);
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ stage kernels
+// Each stage of the chain on its own, for the per-stage operator API.  They share the
+// device functions of the fused kernel, so a stage test also tests the fused path.
+__global__ void k_preemph(const int16_t *x, int16_t *y, long long n, int prev) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int p = i ? (int)x[i - 1] : prev;
+        y[i] = (int16_t)((int)x[i] + (p >> 5) - p);
+    }
+}
+
+__global__ void k_frame(const int16_t *y, int16_t *fr, long long n, long long n_frames) {
+    const long long total = n_frames * NFFT;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long k = i / NFFT, s = k * HOP + (i - k * NFFT);
+        fr[i] = s < n ? y[s] : (int16_t)0;
+    }
+}
+
+__global__ void k_window(const int16_t *fr, int16_t *w, long long n_frames, const DevTables *tab) {
+    const long long total = n_frames * NFFT;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+        w[i] = (int16_t)(((int)fr[i] * (int)tab->curve[i & (NFFT - 1)]) >> 9);
+}
+
+__global__ void k_power(const int16_t *f, uint32_t *pw, long long n_frames) {
+    const long long total = n_frames * NBINS;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int re = f[2 * i], im = f[2 * i + 1];
+        pw[i] = ((unsigned)(re * re) + (unsigned)(im * im)) >> 2;
+    }
+}
+
+__global__ void k_log2(const uint16_t *m, uint16_t *o, long long total) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+        o[i] = (uint16_t)log2fix_lane(m[i]);
+}
+
+struct StageSmem {
+    DevTables tab;
+    alignas(16) unsigned xbuf[WARPS][XW];
+};
+
+// warp-per-frame stages: FFT, MEL, DCT
+template <int STAGE, int NF>
+__global__ void __launch_bounds__(THREADS) k_warp_stage(const void *in, void *out, long long n_frames, const DevTables *gtab)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    StageSmem *sm = reinterpret_cast<StageSmem *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const int4 *src = reinterpret_cast<const int4 *>(gtab);
+        int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
+        for (int i = tid; i < (int)(sizeof(DevTables) / 16); i += THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    unsigned *xbuf = sm->xbuf[warp];
+    for (long long k = blockIdx.x * (long long)WARPS + warp; k < n_frames; k += (long long)gridDim.x * WARPS) {
+        if (STAGE == MFCC_B200_STAGE_FFT) {
+            const int16_t *w = reinterpret_cast<const int16_t *>(in) + k * NFFT;
+            int16_t *o = reinterpret_cast<int16_t *>(out) + k * NBINS * 2;
+            const int bt = (int)(__brev((unsigned)lane) >> 27);
+            int xr[16], re[8], im[8];
+#pragma unroll
+            for (int l = 0; l < 16; ++l) xr[l] = w[bt + 32 * brev4(l)];
+            fft512_warp(xr, xbuf, &sm->tab, lane, re, im);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int b = lane + 32 * i;
+                o[2 * b] = (int16_t)re[i]; o[2 * b + 1] = (int16_t)im[i];
+            }
+        } else if (STAGE == MFCC_B200_STAGE_MEL) {
+            const uint32_t *pw = reinterpret_cast<const uint32_t *>(in) + k * NBINS;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xbuf[lane + 32 * i] = pw[lane + 32 * i];
+            __syncwarp();
+            const unsigned mel = mel_warp<NF>(xbuf, &sm->tab, lane);
+            __syncwarp();
+            if (lane < NF) reinterpret_cast<uint16_t *>(out)[k * NF + lane] = (uint16_t)mel;
+        } else {
+            const uint16_t *lg = reinterpret_cast<const uint16_t *>(in) + k * NF;
+            const unsigned L = lg[lane & (NF - 1)];
+            const int c = dct_warp<NF>(L, &sm->tab, lane);
+            if (lane < NF) reinterpret_cast<int16_t *>(out)[k * NF + lane] = (int16_t)c;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ streaming step
+// One hop per stream: state = [prev | nfft-hop raw samples], see include/mfcc_b200.h.
+constexpr int STATE_N = NFFT - HOP + 2;      // 344 int16 per stream (343 used, even pitch)
+
+struct StepSmem {
+    DevTables tab;
+    alignas(16) int16_t pre[WARPS][NFFT];
+    alignas(16) unsigned xbuf[WARPS][XW];
+};
+
+template <int NF>
+__global__ void __launch_bounds__(THREADS) mfcc_int_step(int16_t *state, const int16_t *hop, int n_streams,
+                                                         int16_t *out, int nceptrums, const DevTables *gtab)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    StepSmem *sm = reinterpret_cast<StepSmem *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const int4 *src = reinterpret_cast<const int4 *>(gtab);
+        int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
+        for (int i = tid; i < (int)(sizeof(DevTables) / 16); i += THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    const mfcc_b200_taps none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    for (int s = blockIdx.x * WARPS + warp; s < n_streams; s += gridDim.x * WARPS) {
+        int16_t *st = state + (long long)s * STATE_N;     // st[0] = prev, st[1..342] = history
+        const int16_t *hp = hop + (long long)s * HOP;
+        int16_t *pre = sm->pre[warp];
+        constexpr int HIST = NFFT - HOP;                  // 342
+        // raw(n) for n = -1 .. 511: state then hop
+        int16_t nv[11];                                   // this lane's share of the new state
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            const int n = lane + 32 * r;
+            const int cur = n < HIST ? st[1 + n] : hp[n - HIST];
+            const int prv = n <= HIST ? st[n] : hp[n - 1 - HIST];
+            pre[n] = (int16_t)(cur + (prv >> 5) - prv);
+        }
+        // new state = raw[HOP-1 .. 511]
+#pragma unroll
+        for (int r = 0; r < 11; ++r) {
+            const int i = lane + 32 * r;                  // 0..342
+            const int n = i + HOP - 1;
+            nv[r] = (i <= HIST) ? (n < HIST ? st[1 + n] : hp[n - HIST]) : (int16_t)0;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < 11; ++r) {
+            const int i = lane + 32 * r;
+            if (i <= HIST) st[i] = nv[r];
+        }
+        frame_warp<NF>(pre, sm->xbuf[warp], &sm->tab, lane, out + (long long)s * nceptrums, nceptrums, none, 0);
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------ host side
+thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CUDA_TRY(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t e_ = (expr);                                                               \
+        if (e_ != cudaSuccess)                                                                 \
+            return fail(MFCC_B200_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));  \
+    } while (0)
+
+struct Handle {
+    mfcc_b200_cfg cfg;
+    DevTables *d_tab = nullptr;
+    int device = 0;
+    int sm_count = 0;
+    // staging for mfcc_b200_run_host
+    cudaStream_t st[2] = {nullptr, nullptr};
+    int16_t *d_in[2] = {nullptr, nullptr};
+    int16_t *d_out[2] = {nullptr, nullptr};
+    size_t in_cap = 0, out_cap = 0;
+};
+
+// Which twiddle each DCT lane needs: ownership of positions through the 2NF-point
+// sub-FFT (mirrors tests/lane_model.py: dct_plan).
+int build_dct_plan(int nf, const int32_t *tw /* [2nf][2] */, DevTables &t) {
+    int S = 0;
+    while ((1 << S) < 2 * nf) ++S;
+    std::vector<int> A(nf), x0(nf);
+    for (int j = 0; j < nf; ++j) A[j] = 2 * j;
+    for (int s = 1; s < S; ++s) {
+        for (int j = 0; j < nf; ++j) {
+            const int bit = (j >> (s - 1)) & 1, partner = j ^ (1 << (s - 1));
+            if (!bit && A[partner] != A[j] + (1 << s)) return -1;
+            x0[j] = bit ? A[partner] + (1 << (s - 1)) : A[j];
+        }
+        for (int j = 0; j < nf; ++j) {
+            const int k = x0[j] % (1 << s);
+            const int idx = k * ((2 * nf) >> s);
+            t.dct_tw[s * 32 + j] = make_int2(2 * tw[2 * idx], 2 * tw[2 * idx + 1]);
+        }
+        A = x0;
+    }
+    for (int j = 0; j < nf; ++j) {
+        if (A[j] != j) return -1;                   // lane j must own bin j
+        t.dct_twf[j] = make_int2(2 * tw[2 * j], 2 * tw[2 * j + 1]);
+    }
+    return 0;
+}
+
+int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
+    memset(&t, 0, sizeof(t));
+    const int32_t *tw = c.tw_fft;
+    for (int k = 0; k < 8; ++k)
+        if (tw[2 * 32 * k] != H_TWA_RE[k] || tw[2 * 32 * k + 1] != H_TWA_IM[k])
+            return fail(MFCC_B200_EUNSUPPORTED, "tw_fft does not match the twiddles compiled into stages 0-3");
+    auto dbl = [&](int idx) { return make_int2(2 * tw[2 * idx], 2 * tw[2 * idx + 1]); };
+    for (int l = 0; l < 16; ++l) {
+        t.twB[l] = dbl(16 * l);                                     // stage 4
+        t.twB[16 + l] = dbl(8 * l);                                 // stage 5
+        for (int mm = 0; mm < 2; ++mm) t.twB[32 + mm * 16 + l] = dbl(64 * mm + 4 * l);   // stage 6
+        for (int mm = 0; mm < 4; ++mm) t.twB[64 + mm * 16 + l] = dbl(32 * mm + 2 * l);   // stage 7
+    }
+    // the -j rotation used for the upper half of stages 5..7 must agree with the ROM
+    for (int k = 0; k < 128; ++k)
+        if (tw[2 * (k + 128)] != tw[2 * k + 1] || tw[2 * (k + 128) + 1] != -tw[2 * k])
+            return fail(MFCC_B200_EUNSUPPORTED, "tw_fft is not a quarter-circle decode (fft.py:55-59)");
+    for (int b = 0; b < 256; ++b) t.tw8[b] = dbl(b);
+    for (int n = 0; n < NFFT; ++n) {
+        if (c.window_curve[n] < 0 || c.window_curve[n] > 511)
+            return fail(MFCC_B200_EUNSUPPORTED, "window_curve out of the 9-bit range");
+        t.curve[n] = (int16_t)c.window_curve[n];
+    }
+    int g = 0, first = 0;
+    for (int b = 0; b < NBINS; ++b) {
+        if (c.mel_weight[b] >> 30) return fail(MFCC_B200_EUNSUPPORTED, "mel_weight wider than 30 bits");
+        t.melw[b] = c.mel_weight[b];
+        if (c.mel_close[b]) {
+            if (g >= 40) return fail(MFCC_B200_EUNSUPPORTED, "too many mel segments");
+            t.seg_first[g] = (int16_t)first;
+            t.seg_close[g] = (int16_t)b;
+            first = b + 1;
+            ++g;
+        }
+    }
+    if (g != c.nfilters + 1 || first != NBINS)
+        return fail(MFCC_B200_EUNSUPPORTED, "mel tables must describe nfilters+1 segments ending at the last bin");
+    t.nseg = g;
+    t.mel_lo_bit = c.mel_lo_bit;
+    if (build_dct_plan(c.nfilters, c.tw_dct, t) != 0)
+        return fail(MFCC_B200_EUNSUPPORTED, "internal: DCT lane plan failed");
+    return MFCC_B200_OK;
+}
+
+template <typename K>
+int set_smem(K kernel, size_t bytes) {
+    CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return MFCC_B200_OK;
+}
+
+int check_handle(void *h) {
+    if (!h) return fail(MFCC_B200_EINVAL, "null handle");
+    return MFCC_B200_OK;
+}
+
+inline int grid_1d(long long total, int block, int sm_count) {
+    long long g = (total + block - 1) / block;
+    const long long cap = (long long)sm_count * 16;
+    if (g > cap) g = cap;
+    return g < 1 ? 1 : (int)g;
+}
+
+}  // namespace
+
+// =================================================================== C ABI
+extern "C" {
+
+int mfcc_b200_version(void) { return 1; }
+const char *mfcc_b200_last_error(void) { return g_err.c_str(); }
+int64_t mfcc_b200_launch_count(void) { return g_launches.load(); }
+
+int mfcc_b200_create(const mfcc_b200_cfg *cfg, void **handle)
+{
+    if (!cfg || !handle) return fail(MFCC_B200_EINVAL, "null argument");
+    *handle = nullptr;
+    if (cfg->struct_size != (int32_t)sizeof(mfcc_b200_cfg)) return fail(MFCC_B200_EINVAL, "mfcc_b200_cfg size mismatch");
+    if (cfg->mode != MFCC_B200_MODE_INT) return fail(MFCC_B200_EUNSUPPORTED, "only MFCC_B200_MODE_INT is built so far");
+    if (cfg->nfft != NFFT || cfg->hop != HOP) return fail(MFCC_B200_EUNSUPPORTED, "kernels cover nfft=512, hop=170");
+    if (cfg->nfilters != 16 && cfg->nfilters != 32) return fail(MFCC_B200_EUNSUPPORTED, "kernels cover nfilters 16 and 32");
+    if (cfg->nceptrums < 1 || cfg->nceptrums > cfg->nfilters) return fail(MFCC_B200_EINVAL, "nceptrums out of range");
+    if (cfg->window_shift != 9 || cfg->pow_shift != 2 || cfg->mel_wbits != 30 || cfg->mel_out_bits != 16 ||
+        cfg->log_precision != 11 || cfg->log_out_bits != 15)
+        return fail(MFCC_B200_EUNSUPPORTED, "kernels cover the widths MFCC.elaborate uses (mfcc/core/mfcc.py:38-88)");
+    if (cfg->mel_lo_bit < 30 || cfg->mel_lo_bit > 40) return fail(MFCC_B200_EUNSUPPORTED, "mel_lo_bit out of range");
+    if (!cfg->window_curve || !cfg->tw_fft || !cfg->tw_dct || !cfg->mel_weight || !cfg->mel_close)
+        return fail(MFCC_B200_EINVAL, "missing table");
+
+    Handle *h = new Handle();
+    h->cfg = *cfg;
+    h->cfg.window_curve = nullptr; h->cfg.tw_fft = nullptr; h->cfg.tw_dct = nullptr;
+    h->cfg.mel_weight = nullptr; h->cfg.mel_close = nullptr;
+    DevTables t;
+    int rc = build_tables(*cfg, t);
+    if (rc) { delete h; return rc; }
+    cudaError_t e = cudaGetDevice(&h->device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_tab, sizeof(DevTables));
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_tab, &t, sizeof(DevTables), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        if (h->d_tab) cudaFree(h->d_tab);
+        delete h;
+        return fail(MFCC_B200_ECUDA, std::string("mfcc_b200_create: ") + cudaGetErrorString(e));
+    }
+    rc = set_smem(mfcc_int_fused<32>, sizeof(Smem));
+    if (!rc) rc = set_smem(mfcc_int_fused<16>, sizeof(Smem));
+    if (!rc) rc = set_smem(mfcc_int_step<32>, sizeof(StepSmem));
+    if (!rc) rc = set_smem(mfcc_int_step<16>, sizeof(StepSmem));
+    if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_FFT, 32>, sizeof(StageSmem));
+    if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_MEL, 32>, sizeof(StageSmem));
+    if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_MEL, 16>, sizeof(StageSmem));
+    if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_DCT, 32>, sizeof(StageSmem));
+    if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_DCT, 16>, sizeof(StageSmem));
+    if (rc) { cudaFree(h->d_tab); delete h; return rc; }
+    *handle = h;
+    return MFCC_B200_OK;
+}
+
+void mfcc_b200_destroy(void *handle)
+{
+    Handle *h = static_cast<Handle *>(handle);
+    if (!h) return;
+    for (int i = 0; i < 2; ++i) {
+        if (h->st[i]) cudaStreamDestroy(h->st[i]);
+        if (h->d_in[i]) cudaFree(h->d_in[i]);
+        if (h->d_out[i]) cudaFree(h->d_out[i]);
+    }
+    if (h->d_tab) cudaFree(h->d_tab);
+    delete h;
+}
+
+int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t n_samples, int32_t n_clips,
+                  int64_t n_frames, void *d_out, int64_t out_clip_stride, const mfcc_b200_taps *taps, void *stream)
+{
+    if (int rc = check_handle(handle)) return rc;
+    Handle *h = static_cast<Handle *>(handle);
+    if (n_clips < 0 || n_frames < 0 || n_samples < 0) return fail(MFCC_B200_EINVAL, "negative size");
+    if (n_clips == 0 || n_frames == 0) return MFCC_B200_OK;
+    if (!d_x || !d_out) return fail(MFCC_B200_EINVAL, "null buffer");
+    if (n_clips > 1 && (clip_stride < n_samples || out_clip_stride < n_frames * h->cfg.nceptrums))
+        return fail(MFCC_B200_EINVAL, "row pitch smaller than the row");
+    if (taps && n_clips != 1) return fail(MFCC_B200_EINVAL, "taps need n_clips == 1");
+    if (HOP * (n_frames - 1) + NFFT > (1LL << 40)) return fail(MFCC_B200_EINVAL, "clip too long");
+
+    RunParams p;
+    memset(&p, 0, sizeof(p));
+    p.x = d_x; p.clip_stride = clip_stride; p.n_samples = n_samples; p.n_frames = n_frames;
+    p.out = static_cast<int16_t *>(d_out); p.out_clip_stride = out_clip_stride;
+    p.tab = h->d_tab; p.nceptrums = h->cfg.nceptrums;
+    p.tiles_per_clip = (int)((n_frames + FT - 1) / FT);
+    p.n_tiles = (long long)p.tiles_per_clip * n_clips;
+    p.aligned = ((reinterpret_cast<uintptr_t>(d_x) & 15) == 0) && (n_clips == 1 || (clip_stride % 8) == 0);
+    if (taps) p.taps = *taps;
+    long long grid = (long long)h->sm_count * CTAS_PER_SM;
+    if (grid > p.n_tiles) grid = p.n_tiles;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (h->cfg.nfilters == 32) mfcc_int_fused<32><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+    else                       mfcc_int_fused<16><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+    g_launches.fetch_add(1);
+    CUDA_TRY(cudaGetLastError());
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, int64_t n_samples, int32_t n_clips,
+                       int64_t n_frames, void *h_out, int64_t out_clip_stride)
+{
+    if (int rc = check_handle(handle)) return rc;
+    Handle *h = static_cast<Handle *>(handle);
+    if (n_clips < 0 || n_frames < 0 || n_samples < 0) return fail(MFCC_B200_EINVAL, "negative size");
+    if (n_clips == 0 || n_frames == 0) return MFCC_B200_OK;
+    if (!h_x || !h_out) return fail(MFCC_B200_EINVAL, "null buffer");
+    if (n_clips > 1 && (clip_stride < n_samples || out_clip_stride < n_frames * h->cfg.nceptrums))
+        return fail(MFCC_B200_EINVAL, "row pitch smaller than the row");
+    const int nc = h->cfg.nceptrums;
+    const long long in_row = n_samples ? ((n_samples + 7) & ~7LL) : 8;   // device row pitch: 16-byte multiple (TMA)
+    const long long out_row = n_frames * nc;
+    // chunks of clips sized for ~32 MiB of samples; two streams alternate so that the
+    // copy-in of one chunk, the kernel of another and the copy-out overlap on PCIe
+    long long per = (32LL << 20) / (in_row * 2);
+    if (per < 1) per = 1;
+    if (per > n_clips) per = n_clips;
+    const size_t in_need = (size_t)per * in_row * 2, out_need = (size_t)per * out_row * 2;
+    if (in_need > h->in_cap || out_need > h->out_cap) {
+        for (int i = 0; i < 2; ++i) {
+            if (h->d_in[i]) cudaFree(h->d_in[i]);
+            if (h->d_out[i]) cudaFree(h->d_out[i]);
+            h->d_in[i] = h->d_out[i] = nullptr;
+        }
+        h->in_cap = h->out_cap = 0;
+        for (int i = 0; i < 2; ++i) {
+            if (!h->st[i]) CUDA_TRY(cudaStreamCreateWithFlags(&h->st[i], cudaStreamNonBlocking));
+            CUDA_TRY(cudaMalloc(&h->d_in[i], in_need));
+            CUDA_TRY(cudaMalloc(&h->d_out[i], out_need));
+        }
+        h->in_cap = in_need; h->out_cap = out_need;
+    }
+    int16_t *out16 = static_cast<int16_t *>(h_out);
+    int slot = 0;
+    for (long long done = 0; done < n_clips; slot ^= 1) {
+        const long long n = (n_clips - done) < per ? (n_clips - done) : per;
+        cudaStream_t s = h->st[slot];
+        // straight from / to the caller's buffers: full PCIe rate when they are pinned
+        if (n_samples)
+            CUDA_TRY(cudaMemcpy2DAsync(h->d_in[slot], (size_t)in_row * 2, h_x + done * clip_stride, (size_t)clip_stride * 2,
+                                       (size_t)n_samples * 2, (size_t)n, cudaMemcpyHostToDevice, s));
+        if (int rc = mfcc_b200_run(h, h->d_in[slot], in_row, n_samples, (int32_t)n, n_frames, h->d_out[slot], out_row,
+                                   nullptr, s))
+            return rc;
+        CUDA_TRY(cudaMemcpy2DAsync(out16 + done * out_clip_stride, (size_t)out_clip_stride * 2, h->d_out[slot],
+                                   (size_t)out_row * 2, (size_t)out_row * 2, (size_t)n, cudaMemcpyDeviceToHost, s));
+        done += n;
+    }
+    CUDA_TRY(cudaStreamSynchronize(h->st[0]));
+    CUDA_TRY(cudaStreamSynchronize(h->st[1]));
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_stage(void *handle, int32_t stage, const void *d_in, void *d_out, int64_t n, int64_t n_frames,
+                    int32_t prev, void *stream)
+{
+    if (int rc = check_handle(handle)) return rc;
+    Handle *h = static_cast<Handle *>(handle);
+    if (stage < 0 || stage >= MFCC_B200_STAGE_COUNT) return fail(MFCC_B200_EINVAL, "unknown stage");
+    if (n < 0 || n_frames < 0) return fail(MFCC_B200_EINVAL, "negative size");
+    const long long rows = (stage == MFCC_B200_STAGE_FRAME) ? n_frames : n;
+    if (rows == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out) return fail(MFCC_B200_EINVAL, "null buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int nf = h->cfg.nfilters;
+    const int B = 256;
+    switch (stage) {
+    case MFCC_B200_STAGE_PREEMPH:
+        k_preemph<<<grid_1d(n, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, prev);
+        break;
+    case MFCC_B200_STAGE_FRAME:
+        k_frame<<<grid_1d(n_frames * NFFT, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, n_frames);
+        break;
+    case MFCC_B200_STAGE_WINDOW:
+        k_window<<<grid_1d(n * NFFT, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, h->d_tab);
+        break;
+    case MFCC_B200_STAGE_POWER:
+        k_power<<<grid_1d(n * NBINS, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (uint32_t *)d_out, n);
+        break;
+    case MFCC_B200_STAGE_LOG2:
+        k_log2<<<grid_1d(n * nf, B, h->sm_count), B, 0, s>>>((const uint16_t *)d_in, (uint16_t *)d_out, n * nf);
+        break;
+    default: {
+        const int grid = grid_1d(n, WARPS, h->sm_count);
+        if (stage == MFCC_B200_STAGE_FFT)
+            k_warp_stage<MFCC_B200_STAGE_FFT, 32><<<grid, THREADS, sizeof(StageSmem), s>>>(d_in, d_out, n, h->d_tab);
+        else if (stage == MFCC_B200_STAGE_MEL && nf == 32)
+            k_warp_stage<MFCC_B200_STAGE_MEL, 32><<<grid, THREADS, sizeof(StageSmem), s>>>(d_in, d_out, n, h->d_tab);
+        else if (stage == MFCC_B200_STAGE_MEL)
+            k_warp_stage<MFCC_B200_STAGE_MEL, 16><<<grid, THREADS, sizeof(StageSmem), s>>>(d_in, d_out, n, h->d_tab);
+        else if (nf == 32)
+            k_warp_stage<MFCC_B200_STAGE_DCT, 32><<<grid, THREADS, sizeof(StageSmem), s>>>(d_in, d_out, n, h->d_tab);
+        else
+            k_warp_stage<MFCC_B200_STAGE_DCT, 16><<<grid, THREADS, sizeof(StageSmem), s>>>(d_in, d_out, n, h->d_tab);
+    }
+    }
+    g_launches.fetch_add(1);
+    CUDA_TRY(cudaGetLastError());
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_state_bytes(void *handle, int32_t n_streams, int64_t *bytes)
+{
+    if (int rc = check_handle(handle)) return rc;
+    if (!bytes || n_streams < 0) return fail(MFCC_B200_EINVAL, "bad argument");
+    *bytes = (int64_t)n_streams * STATE_N * (int64_t)sizeof(int16_t);
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n_streams, void *d_out, void *stream)
+{
+    if (int rc = check_handle(handle)) return rc;
+    Handle *h = static_cast<Handle *>(handle);
+    if (n_streams < 0) return fail(MFCC_B200_EINVAL, "negative size");
+    if (n_streams == 0) return MFCC_B200_OK;
+    if (!d_state || !d_hop || !d_out) return fail(MFCC_B200_EINVAL, "null buffer");
+    int grid = (n_streams + WARPS - 1) / WARPS;
+    const int cap = h->sm_count * 8;
+    if (grid > cap) grid = cap;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (h->cfg.nfilters == 32)
+        mfcc_int_step<32><<<grid, THREADS, sizeof(StepSmem), s>>>((int16_t *)d_state, d_hop, n_streams, (int16_t *)d_out,
+                                                                   h->cfg.nceptrums, h->d_tab);
+    else
+        mfcc_int_step<16><<<grid, THREADS, sizeof(StepSmem), s>>>((int16_t *)d_state, d_hop, n_streams, (int16_t *)d_out,
+                                                                   h->cfg.nceptrums, h->d_tab);
+    g_launches.fetch_add(1);
+    CUDA_TRY(cudaGetLastError());
+    return MFCC_B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,227 @@
+"""One callable per stage module of the reference, same constructor names and
+defaults; each maps a GPU tensor to a GPU tensor through
+``mfcc_b200_stage``.  Only the parameter combinations MFCC.elaborate can generate
+(/root/reference/mfcc/core/mfcc.py:38-88) have a CUDA path; others raise ValueError.
+
+16-bit unsigned streams (mel, log) are carried in int16 tensors and 30-bit powers in
+int32 tensors: same bits, torch has no general uint16/uint32 arithmetic.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from .config import MFCCConfig
+from .handle import Handle
+
+
+class _Stage:
+    stage_id = -1
+
+    def _setup(self, handle, device, nfilters=32):
+        if not torch.cuda.is_available():
+            raise RuntimeError("stage operators need a CUDA device: there is no CPU fallback")
+        self.device = torch.device(device if device is not None else
+                                   "cuda:%d" % torch.cuda.current_device())
+        if handle is None:
+            with torch.cuda.device(self.device):
+                handle = Handle(MFCCConfig(nfilters=nfilters, nceptrums=nfilters))
+        self._h = handle
+
+    def _check(self, x, dtype, last_dims):
+        if not isinstance(x, torch.Tensor) or x.dtype != dtype:
+            raise TypeError("%s takes a %s tensor" % (type(self).__name__, dtype))
+        if x.device != self.device:
+            raise ValueError("input is on %s, operator on %s" % (x.device, self.device))
+        if tuple(x.shape[-len(last_dims):]) != tuple(last_dims):
+            raise ValueError("%s: trailing dimensions must be %s" % (type(self).__name__,
+                                                                      (last_dims,)))
+        return x.contiguous()
+
+    def _run(self, x, out, n, n_frames=0, prev=0):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_stage(
+                self._h.ptr, self.stage_id, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()),
+                n, n_frames, prev, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
+
+
+class Preemph(_Stage):
+    """Preemph(width=16), mfcc/core/preemph.py:9-30.  int16 [N] -> int16 [N]."""
+    stage_id = _lib.STAGE_PREEMPH
+
+    def __init__(self, width=16, _handle=None, device=None):
+        if width != 16:
+            raise ValueError("width must be 16")
+        self.width = width
+        self._setup(_handle, device)
+
+    def __call__(self, x, prev=0):
+        if x.dim() != 1:
+            raise ValueError("Preemph takes one stream [N]")
+        x = self._check(x, torch.int16, (x.shape[-1],))
+        return self._run(x, torch.empty_like(x), x.numel(), 0, int(prev))
+
+
+class Frame(_Stage):
+    """Frame(width=16, windowlen=400, stepsize=160, nfft=512), mfcc/core/frame.py:49-60.
+    int16 [N] -> int16 [K, nfft]; K = full frames unless n_frames is given (zero-extended)."""
+    stage_id = _lib.STAGE_FRAME
+
+    def __init__(self, width=16, windowlen=400, stepsize=160, nfft=512, _handle=None, device=None):
+        if windowlen > nfft:
+            raise ValueError("windowlen must be <= nfft")          # frame.py:51
+        if (width, windowlen, stepsize, nfft) != (16, 512, 170, 512):
+            raise ValueError("CUDA path covers Frame(16, 512, 170, 512) (mfcc.py:41-44)")
+        self.width, self.windowlen, self.stepsize, self.nfft = width, windowlen, stepsize, nfft
+        self._setup(_handle, device)
+
+    def __call__(self, y, n_frames=None):
+        if y.dim() != 1:
+            raise ValueError("Frame takes one stream [N]")
+        y = self._check(y, torch.int16, (y.shape[-1],))
+        n = y.numel()
+        k = (0 if n < self.nfft else (n - self.nfft) // self.stepsize + 1) if n_frames is None \
+            else int(n_frames)
+        out = torch.empty((k, self.nfft), dtype=torch.int16, device=self.device)
+        if k == 0:
+            return out
+        if n == 0:
+            return out.zero_()
+        return self._run(y, out, n, k)
+
+
+class WindowHamming(_Stage):
+    """WindowHamming(width=16, nfft=512, precision=8), mfcc/core/window.py:10-20."""
+    stage_id = _lib.STAGE_WINDOW
+
+    def __init__(self, width=16, nfft=512, precision=8, _handle=None, device=None):
+        if nfft < 8:
+            raise ValueError("nfft must be >= 8")                  # window.py:13
+        if (width, nfft, precision) != (16, 512, 8):
+            raise ValueError("CUDA path covers WindowHamming(16, 512, 8) (mfcc.py:47-49)")
+        self.width, self.nfft, self.precision = width, nfft, precision
+        self._setup(_handle, device)
+
+    def __call__(self, frames):
+        x = self._check(frames, torch.int16, (self.nfft,))
+        return self._run(x, torch.empty_like(x), x.numel() // self.nfft)
+
+
+class FftStream(_Stage):
+    """FftStream(width=16, nfft=512), mfcc/core/fft_stream.py:6-11.
+    int16 [K, 512] -> int16 [K, 256, 2] (data_r, data_i)."""
+    stage_id = _lib.STAGE_FFT
+
+    def __init__(self, width=16, nfft=512, _handle=None, device=None):
+        if nfft <= 0 or nfft & (nfft - 1):
+            raise ValueError("Size must be a positive power-of-two integer, not %r" % (nfft,))
+        if (width, nfft) != (16, 512):
+            raise ValueError("CUDA path covers FftStream(16, 512) (mfcc.py:52-53)")
+        self.width, self.nfft = width, nfft
+        self._setup(_handle, device)
+
+    def __call__(self, frames):
+        x = self._check(frames, torch.int16, (self.nfft,))
+        out = torch.empty(x.shape[:-1] + (self.nfft // 2, 2), dtype=torch.int16, device=self.device)
+        return self._run(x, out, x.numel() // self.nfft)
+
+
+class PowerSpectrum(_Stage):
+    """PowerSpectrum(width=16, width_output=24), mfcc/core/pow2.py:43-50.
+    int16 [K, 256, 2] -> int32 [K, 256] (30-bit unsigned values)."""
+    stage_id = _lib.STAGE_POWER
+
+    def __init__(self, width=16, width_output=24, multiplier_cls=None, _handle=None, device=None):
+        if (width, width_output) != (16, 30):
+            raise ValueError("CUDA path covers PowerSpectrum(16, 30) (mfcc.py:60-62)")
+        self.width, self.width_output = width, width_output
+        self._setup(_handle, device)
+
+    def __call__(self, spec):
+        x = self._check(spec, torch.int16, (256, 2))
+        out = torch.empty(x.shape[:-1], dtype=torch.int32, device=self.device)
+        return self._run(x, out, x.numel() // 512)
+
+
+class FilterBank(_Stage):
+    """FilterBank(width=24, width_output=24, width_mul=None, gain=0, sample_rate=16000,
+    nfft=512, ntap=16), mfcc/core/filterbank.py:37-63.  int32 [K, 256] -> int16 [K, ntap]
+    (16-bit unsigned values that wrap, filterbank.py:122)."""
+    stage_id = _lib.STAGE_MEL
+
+    def __init__(self, width=24, width_output=24, width_mul=None, gain=0, sample_rate=16000,
+                 nfft=512, ntap=16, multiplier_cls=None, _handle=None, device=None):
+        width_mul = width if width_mul is None else width_mul
+        if (width, width_output, width_mul, gain, nfft) != (30, 16, 30, 18, 512) or \
+                ntap not in (16, 32):
+            raise ValueError("CUDA path covers FilterBank(30, 16, gain=18, nfft=512, ntap 16|32) "
+                             "(mfcc.py:69-75)")
+        self.width, self.width_output, self.width_mul, self.gain = width, width_output, width_mul, gain
+        self.sample_rate, self.nfft, self.ntap = sample_rate, nfft, ntap
+        if _handle is not None and (_handle.cfg.nfilters != ntap or
+                                    _handle.cfg.samplerate != sample_rate):
+            _handle = None
+        if _handle is None and torch.cuda.is_available():
+            dev = torch.device(device if device is not None else
+                               "cuda:%d" % torch.cuda.current_device())
+            with torch.cuda.device(dev):
+                _handle = Handle(MFCCConfig(samplerate=sample_rate, nfilters=ntap, nceptrums=ntap))
+        self._setup(_handle, device, ntap)
+
+    def __call__(self, power):
+        x = self._check(power, torch.int32, (256,))
+        out = torch.empty(x.shape[:-1] + (self.ntap,), dtype=torch.int16, device=self.device)
+        return self._run(x, out, x.numel() // 256)
+
+
+class Log2Fix(_Stage):
+    """Log2Fix(width, width_output), mfcc/core/log.py:107-116.  Elementwise,
+    int16 (16-bit unsigned) -> int16 (Q4.11)."""
+    stage_id = _lib.STAGE_LOG2
+
+    def __init__(self, width, width_output, multiplier_cls=None, _handle=None, device=None):
+        if (width, width_output) != (16, 15):
+            raise ValueError("CUDA path covers Log2Fix(16, 15) (mfcc.py:82)")
+        self.width, self.width_output = width, width_output
+        self.precision = 11
+        self._setup(_handle, device)
+
+    def __call__(self, mel):
+        nf = self._h.cfg.nfilters
+        if mel.numel() % nf:
+            raise ValueError("Log2Fix: element count must be a multiple of nfilters=%d" % nf)
+        x = self._check(mel, torch.int16, (mel.shape[-1],))
+        return self._run(x, torch.empty_like(x), x.numel() // nf)
+
+
+class DCTStream(_Stage):
+    """DCTStream(width=16, nfft=16), mfcc/core/dct_stream.py:6-11 (nfft = number of
+    inputs).  int16 [K, nfft] -> int16 [K, nfft]."""
+    stage_id = _lib.STAGE_DCT
+
+    def __init__(self, width=16, nfft=16, _handle=None, device=None):
+        if width != 16 or nfft not in (16, 32):
+            raise ValueError("CUDA path covers DCTStream(16, 16|32) (mfcc.py:84)")
+        self.width, self.nfft = width, nfft
+        if _handle is not None and _handle.cfg.nfilters != nfft:
+            _handle = None
+        self._setup(_handle, device, nfft)
+
+    def __call__(self, logs):
+        x = self._check(logs, torch.int16, (self.nfft,))
+        return self._run(x, torch.empty_like(x), x.numel() // self.nfft)
+
+
+class Discard:
+    """Discard(width=16, first=0, count=16), mfcc/misc/discard.py:5-13: keeps elements
+    first .. first+count-1 of each row.  A view; no kernel."""
+
+    def __init__(self, width=16, first=0, count=16):
+        self.width, self.first, self.count = width, first, count
+        self.last = first + count - 1
+
+    def __call__(self, x):
+        return x[..., self.first: self.first + self.count]

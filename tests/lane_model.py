@@ -1,0 +1,231 @@
+"""Lane-level model of the fused CUDA kernel (mfcc_b200/csrc/mfcc_kernels.cu).
+
+One warp (32 lanes) computes one frame.  This file mirrors the kernel's data
+movement step by step in numpy (registers = arrays indexed [lane, slot], shared
+memory = flat arrays, shuffles = fancy indexing) so that the index arithmetic of
+the design -- bit-reversed loads, the two shared-memory exchanges and their bank
+skews, per-lane twiddle indices, the shuffle plan of the DCT -- can be checked
+against the oracle on a machine without a GPU (tests/test_lane_model.py).
+
+It is a test aid, not product code.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from mfcc_b200 import tables as T
+
+LANES = 32
+
+
+def brev(v, bits):
+    r = 0
+    for _ in range(bits):
+        r = (r << 1) | (v & 1)
+        v >>= 1
+    return r
+
+
+def s16(v):
+    return ((np.asarray(v, dtype=np.int64) + 32768) & 0xFFFF) - 32768
+
+
+def s32(v):
+    return ((np.asarray(v, dtype=np.int64) + (1 << 31)) & 0xFFFFFFFF) - (1 << 31)
+
+
+def bfly(x0r, x0i, x1r, x1i, wr, wi):
+    """The kernel's butterfly: everything doubled so that the result sits in the
+    top half of a 32-bit word and the 32-bit wrap IS the 16-bit wrap of the RTL."""
+    w2r, w2i = 2 * wr, 2 * wi
+    qr = s32(x1r * w2r - x1i * w2i + 16382)
+    qi = s32(x1i * w2r + x1r * w2i + 16382)
+    br = s32(x0r * 32768)
+    bi = s32(x0i * 32768)
+    y0r = s32(br + qr) >> 16
+    y0i = s32(bi + qi) >> 16
+    y1r = s32(br - qr + 32766) >> 16
+    y1i = s32(bi - qi + 32766) >> 16
+    return y0r, y0i, y1r, y1i
+
+
+# ---- exchange address maps (32-bit words inside the per-warp buffer) -------------
+def xa_addr(row, col):
+    """exchange 1: row = lane of pass A (16 positions each), col = slot."""
+    return row * 20 + col + 16 * (row >> 4)
+
+
+def xb_addr(p):
+    """exchange 2: natural position p in 0..511."""
+    return p + 16 * (p >> 8)
+
+
+def bank_conflict_degree(addrs):
+    """max number of distinct words hitting one bank for a warp-wide 32-bit access."""
+    addrs = np.asarray(addrs)
+    worst = 1
+    for b in range(32):
+        words = np.unique(addrs[(addrs % 32) == b])
+        worst = max(worst, len(words))
+    return worst
+
+
+def fft512_frame(w, tw):
+    """w: 512 windowed samples (int).  tw: decoded twiddles [256, 2].
+    Returns (re, im) of bins 0..255 and the bank-conflict report."""
+    lane = np.arange(LANES)
+    conflicts = {}
+    # ---- load: slot l of lane t holds position p = 16 t + l = sample brev9(p)
+    xr = np.zeros((LANES, 16), dtype=np.int64)
+    xi = np.zeros((LANES, 16), dtype=np.int64)
+    for l in range(16):
+        n = np.array([brev(int(t), 5) for t in lane]) + 32 * brev(l, 4)
+        assert all(n[t] == brev(16 * t + l, 9) for t in lane)
+        xr[:, l] = w[n]
+        conflicts["load%d" % l] = bank_conflict_degree(n // 2)
+    # ---- pass A: stages 0..3 inside the lane, compile-time twiddles
+    for s in range(4):
+        half = 1 << s
+        for l in range(16):
+            if l & half:
+                continue
+            k = l % half
+            wr, wi = tw[k * (256 >> s)]
+            a, b, c, d = bfly(xr[:, l], xi[:, l], xr[:, l + half], xi[:, l + half], wr, wi)
+            xr[:, l], xi[:, l], xr[:, l + half], xi[:, l + half] = a, b, c, d
+    # ---- exchange 1
+    buf_r = np.zeros(700, dtype=np.int64)
+    buf_i = np.zeros(700, dtype=np.int64)
+    for l in range(16):
+        a = xa_addr(lane, l)
+        buf_r[a], buf_i[a] = xr[:, l], xi[:, l]
+    for q in range(4):   # 128-bit stores are issued per quarter warp
+        for c in range(4):
+            a = xa_addr(lane[8 * c: 8 * c + 8], 4 * q)
+            banks = np.concatenate([(a + i) % 32 for i in range(4)])
+            assert len(np.unique(banks)) == 32, "STS.128 conflict"
+    h = lane >> 4
+    l4 = lane & 15
+    for m in range(16):
+        a = xa_addr(16 * h + m, l4)
+        conflicts["xa_read%d" % m] = bank_conflict_degree(a)
+        xr[:, m], xi[:, m] = buf_r[a], buf_i[a]
+    # lane (h, l4) now holds p = 256 h + 16 m + l4 in slot m
+    # ---- pass B: stages 4..7, twiddle index (p mod 2^s) * (256 >> s)
+    for s in range(4, 8):
+        hm = 1 << (s - 4)
+        for m in range(16):
+            if m & hm:
+                continue
+            k = (m & (hm - 1)) * 16 + l4
+            idx = k * (256 >> s)
+            wr, wi = tw[idx, 0], tw[idx, 1]
+            a, b, c, d = bfly(xr[:, m], xi[:, m], xr[:, m + hm], xi[:, m + hm], wr, wi)
+            xr[:, m], xi[:, m], xr[:, m + hm], xi[:, m + hm] = a, b, c, d
+    # ---- exchange 2
+    for m in range(16):
+        p = 256 * h + 16 * m + l4
+        a = xb_addr(p)
+        conflicts["xb_write%d" % m] = bank_conflict_degree(a)
+        buf_r[a], buf_i[a] = xr[:, m], xi[:, m]
+    re = np.zeros(256, dtype=np.int64)
+    im = np.zeros(256, dtype=np.int64)
+    for i in range(8):
+        b = lane + 32 * i
+        a0, a1 = xb_addr(b), xb_addr(b + 256)
+        conflicts["xb_read%d" % i] = max(bank_conflict_degree(a0), bank_conflict_degree(a1))
+        wr, wi = tw[b, 0], tw[b, 1]
+        y0r, y0i, _, _ = bfly(buf_r[a0], buf_i[a0], buf_r[a1], buf_i[a1], wr, wi)
+        re[b], im[b] = y0r, y0i
+    return re, im, conflicts
+
+
+def mel_lanes(pw, nfilters, samplerate=16e3, nfft=512, lo_bit=31):
+    """Lane g' sums segment g'+off; neighbours exchange (A, peak) by shuffle."""
+    w, seg, close = T.mel_weights(nfilters, nfft, samplerate)
+    bounds = T.mel_segment_bounds(nfilters, nfft, samplerate)
+    nseg = len(bounds)
+    assert nseg == nfilters + 1
+    M64 = (1 << 64) - 1
+    A = [0] * nseg
+    D = [0] * nseg
+    PK = [0] * nseg
+    for g in range(nseg):
+        first, cl = bounds[g]
+        for b in range(first, cl):
+            A[g] = (A[g] + int(pw[b]) * int(w[b])) & M64
+            D[g] = (D[g] + int(pw[b])) & 0xFFFFFFFF
+        PK[g] = int(pw[cl])
+    out = np.zeros(nfilters, dtype=np.int64)
+    for g in range(1, nseg):
+        e = (PK[g - 1] + D[g]) & 0xFFFFFFFF
+        x = (A[g - 1] - A[g] + (e << 30)) & M64
+        out[g - 1] = (x >> lo_bit) & 0xFFFF
+    return out
+
+
+def log2_lane(m, prec=11):
+    """clz-based integer part, then `prec-1` squarings."""
+    m = int(m)
+    mm = max(m, 1)
+    sh = mm.bit_length() - 1
+    z = (mm << prec) >> sh
+    frac = 0
+    for _ in range(prec - 1):
+        c = z * z
+        bit = (c >> (2 * prec + 1)) & 1
+        z = c >> (prec + bit)
+        frac = (frac << 1) | bit
+    return ((sh << prec) + (frac << 1)) & 0x7FFF
+
+
+def dct_plan(nf):
+    """Ownership of positions by lanes through the 2*nf-point sub-FFT (see
+    DESIGN.md, "DCT").  Returns per stage s>=1 the twiddle ROM index of each lane's
+    butterfly and, at the end, the bin each lane owns in slot 0."""
+    S = (2 * nf).bit_length() - 1          # stages of the 2nf-point FFT
+    lanes = np.arange(nf)
+    A = 2 * lanes                          # slot0 position; slot1 = A + 1
+    tw_idx = np.zeros((S, nf), dtype=np.int64)
+    for s in range(1, S):
+        bit = (lanes >> (s - 1)) & 1
+        partner = lanes ^ (1 << (s - 1))
+        # lane with bit 0 takes (A, A + 2^s); lane with bit 1 takes (A_p + 2^(s-1), .. + 2^s)
+        assert np.all(A[partner][bit == 0] == A[bit == 0] + (1 << s))
+        x0pos = np.where(bit == 0, A, A[partner] + (1 << (s - 1)))
+        k = x0pos % (1 << s)
+        tw_idx[s] = k * ((2 * nf) >> s)    # ROM of the 4nf-point FFT has 2nf entries
+        A = x0pos
+    return tw_idx, A
+
+
+def dct_lanes(L, nf, tw):
+    """L: nf log values (lane g holds L[g]).  tw: decoded ROM [2nf, 2] of the 4nf FFT."""
+    S = (2 * nf).bit_length() - 1
+    nb = nf.bit_length() - 1
+    lanes = np.arange(nf)
+    tw_idx, own = dct_plan(nf)
+    src = np.array([brev(int(j), nb) for j in lanes])
+    a = np.asarray(L, dtype=np.int64)[src]                # shuffle
+    b = np.asarray(L, dtype=np.int64)[nf - 1 - src]       # shuffle
+    z = np.zeros(nf, dtype=np.int64)
+    r0, i0, r1, i1 = bfly(a, z, b, z, 16384, 0)           # stage 0
+    for s in range(1, S):
+        bit = (lanes >> (s - 1)) & 1
+        partner = lanes ^ (1 << (s - 1))
+        send_r = np.where(bit == 0, r1, r0)
+        send_i = np.where(bit == 0, i1, i0)
+        rc_r, rc_i = send_r[partner], send_i[partner]     # shuffle xor
+        x0r = np.where(bit == 0, r0, rc_r)
+        x0i = np.where(bit == 0, i0, rc_i)
+        x1r = np.where(bit == 0, rc_r, r1)
+        x1i = np.where(bit == 0, rc_i, i1)
+        wr, wi = tw[tw_idx[s], 0], tw[tw_idx[s], 1]
+        r0, i0, r1, i1 = bfly(x0r, x0i, x1r, x1i, wr, wi)
+    # final stage of the 4nf FFT: even half is all zero, bins own[j] < nf
+    assert sorted(own.tolist()) == list(range(nf))
+    wr, wi = tw[own, 0], tw[own, 1]
+    y, _, _, _ = bfly(z, z, r0, i0, wr, wi)
+    out = np.zeros(nf, dtype=np.int64)
+    out[own] = y
+    return out

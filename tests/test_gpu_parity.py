@@ -1,0 +1,230 @@
+"""GPU parity tests (run on the B200 box): the CUDA path through the C ABI against the
+CPU oracle, bit for bit (integer work: no tolerance)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def RC():
+    from oracle import ref_c
+    return ref_c
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import mfcc_b200
+    return {(nf, nc): mfcc_b200.MFCC(nfilters=nf, nceptrums=nc) for nf, nc in
+            [(32, 32), (32, 16), (16, 16)]}
+
+
+def dev(a, dtype=np.int16):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=dtype)).cuda()
+
+
+def u16(t):
+    return t.cpu().numpy().view(np.uint16)
+
+
+def edge_clips(n=4000, seed=0):
+    rng = np.random.default_rng(seed)
+    t = np.arange(n)
+    return {
+        "noise_full": rng.integers(-32768, 32768, n),
+        "gauss2000": np.clip(rng.normal(0, 2000, n), -32768, 32767),
+        "tones": 8000 * sum(np.sin(2 * np.pi * f * t / 16000) for f in (440.0, 1234.5, 5100.0)) / 3
+                 + rng.normal(0, 50, n),
+        "gated": np.clip(rng.normal(0, 2000, n), -32768, 32767) * ((t // 800) % 2),
+        "zero": np.zeros(n), "max": np.full(n, 32767), "min": np.full(n, -32768),
+        "alt": np.tile([-32768, 32767], n // 2), "dc1": np.ones(n),
+        "impulse": (t == 777) * 32767, "alt4": np.tile([32767, 32767, -32768, -32768], n // 4),
+    }
+
+
+def test_wav_whole_chain_and_taps(ops, RC, wav):
+    m = ops[(32, 32)]
+    cfg = RC.RefConfig(nfilters=32, nceptrums=32)
+    want, tw = RC.run(cfg, wav, taps=True)
+    got, tg = m(dev(wav), taps=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(tg["window"].cpu().numpy(), tw["window"])
+    assert np.array_equal(tg["fft"].cpu().numpy(), tw["fft"])
+    assert np.array_equal(tg["power"].cpu().numpy().view(np.uint32), tw["power"])
+    assert np.array_equal(u16(tg["filter"]), tw["mel"])
+    assert np.array_equal(u16(tg["log"]), tw["log2"])
+    assert np.array_equal(tg["dct"].cpu().numpy(), tw["dct"])
+    assert got.shape == (1046, 32) and np.array_equal(got.cpu().numpy(), want)
+    # and without taps (the production instantiation)
+    assert np.array_equal(m(dev(wav)).cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("key", [(32, 32), (32, 16), (16, 16)])
+def test_edge_clips_batched(ops, RC, key):
+    m = ops[key]
+    cfg = RC.RefConfig(nfilters=key[0], nceptrums=key[1])
+    clips = edge_clips()
+    x = np.stack([np.asarray(v, dtype=np.float64).astype(np.int16) for v in clips.values()])
+    want = RC.run(cfg, x, threads=4)
+    got = m(dev(x)).cpu().numpy()
+    for i, name in enumerate(clips):
+        assert np.array_equal(got[i], want[i]), name
+
+
+@pytest.mark.parametrize("n", [0, 1, 511, 512, 513, 681, 682, 683, 1000, 5951, 5952, 5953, 6121,
+                               6122, 11393, 20001])
+def test_ragged_lengths_and_tile_boundaries(ops, RC, n):
+    """n around nfft, the hop and the 32-frame tile boundary (5952 = 170*32+512)."""
+    m = ops[(32, 32)]
+    cfg = RC.RefConfig()
+    rng = np.random.default_rng(n)
+    x = rng.integers(-32768, 32768, n).astype(np.int16)
+    want = RC.run(cfg, x)
+    got = m(dev(x)).cpu().numpy() if n else np.zeros((0, 32), np.int16)
+    assert got.shape == want.shape and np.array_equal(got, want)
+    # host-protocol frame count: zero-extended tail (software/main.c:95, :135-144)
+    k = m.cfg.num_frames_host(n)
+    if n:
+        want = RC.run(cfg, x, n_frames=k)
+        assert np.array_equal(m(dev(x), n_frames=k).cpu().numpy(), want)
+
+
+def test_unaligned_rows_take_the_plain_load_path(ops, RC):
+    m = ops[(32, 32)]
+    cfg = RC.RefConfig()
+    rng = np.random.default_rng(5)
+    big = rng.integers(-32768, 32768, (3, 7003)).astype(np.int16)   # odd pitch: rows not 16-B aligned
+    want = RC.run(cfg, big)
+    assert np.array_equal(m(dev(big)).cpu().numpy(), want)
+    off = dev(np.concatenate([[0, 0, 0], big[0]]))[3:]              # base pointer off by 6 bytes
+    assert np.array_equal(m(off).cpu().numpy(), want[0])
+
+
+def test_many_clips_full_length(ops, RC):
+    """C2-shaped: 60 s clips, the four synthetic classes of the benchmark."""
+    m = ops[(32, 32)]
+    cfg = RC.RefConfig()
+    import bench
+    x = bench.synth_clips(8, 960000, torch.device("cuda"), first_clip=0)
+    got = m(x).cpu().numpy()
+    want = RC.run(cfg, x.cpu().numpy(), threads=RC.max_threads())
+    assert got.shape == (8, 5645, 32) and np.array_equal(got, want)
+    # the loud class drives the 16-bit mel wrap (filterbank.py:122)
+    _, tp = RC.run(cfg, x[0].cpu().numpy()[:40000], taps=True)
+    assert (tp["mel"] > 0).any()
+
+
+def test_run_host_equals_device_path(ops, RC):
+    m = ops[(32, 16)]
+    cfg = RC.RefConfig(nfilters=32, nceptrums=16)
+    rng = np.random.default_rng(11)
+    x = rng.integers(-20000, 20000, (37, 30001)).astype(np.int16)
+    want = RC.run(cfg, x, threads=4)
+    xh = torch.from_numpy(x).pin_memory()
+    assert np.array_equal(m.run_host(xh).numpy(), want)
+    assert np.array_equal(m.run_host(torch.from_numpy(x)).numpy(), want)     # pageable too
+
+
+# ---- size-independent properties at full scale ---------------------------------------
+def test_properties_at_scale(ops):
+    m = ops[(32, 32)]
+    import bench
+    x = bench.synth_clips(64, 960000, torch.device("cuda"), first_clip=0)
+    a = m(x)
+    # determinism / idempotence
+    assert torch.equal(a, m(x))
+    # clips are independent: a permutation of the batch permutes the result
+    perm = torch.randperm(64, device="cuda")
+    assert torch.equal(m(x[perm].contiguous()), a[perm])
+    # frame k depends only on samples 170k-1 .. 170k+511: a window cut out of a clip
+    # (with its predecessor sample zeroed by the cut) agrees from its second frame on
+    cut = x[3, 170 * 100:170 * 100 + 170 * 40 + 512].contiguous()
+    b = m(cut)
+    assert torch.equal(b[1:], a[3, 101:141])
+    # silence -> log2(0) := 0 everywhere -> all-zero cepstra
+    z = torch.zeros(5000, dtype=torch.int16, device="cuda")
+    assert int(m(z).abs().max()) == 0
+
+
+# ---- per-stage operators -------------------------------------------------------------
+def test_stage_operators(ops, RC, wav):
+    from oracle import ref_np as R
+    m = ops[(32, 32)]
+    x = wav[:30000]
+    _, tp = R.mfcc(x, nfilters=32, nceptrums=32, taps=True)
+    y = m.preemph(dev(x))
+    assert np.array_equal(y.cpu().numpy(), tp["preemph"])
+    fr = m.frame(y)
+    assert np.array_equal(fr.cpu().numpy(), tp["frame"])
+    assert np.array_equal(m.frame(y, n_frames=fr.shape[0] + 3).cpu().numpy()[-1, -170:], np.zeros(170))
+    w = m.window(fr)
+    assert np.array_equal(w.cpu().numpy(), tp["window"])
+    f = m.fft_stream(w)
+    assert np.array_equal(f.cpu().numpy()[..., 0], tp["fft_r"]) and np.array_equal(f.cpu().numpy()[..., 1], tp["fft_i"])
+    p = m.powspec(f)
+    assert np.array_equal(p.cpu().numpy().view(np.uint32), tp["power"])
+    mel = m.filterbank(p)
+    assert np.array_equal(u16(mel), tp["filter"])
+    lg = m.log2(mel)
+    assert np.array_equal(u16(lg), tp["log"])
+    d = m.dct_stream(lg)
+    assert np.array_equal(d.cpu().numpy(), tp["dct"])
+    assert np.array_equal(m.discard(d).cpu().numpy(), tp["dct"][:, :32])
+    # arbitrary (not chain-produced) inputs, including full-scale wrap cases
+    rng = np.random.default_rng(2)
+    fr2 = rng.integers(-32768, 32768, (50, 512)).astype(np.int16)
+    fr2[0] = np.tile([-32768, 32767], 256)
+    rr, ri = R.fft_stream(fr2)
+    f2 = m.fft_stream(dev(fr2)).cpu().numpy()
+    assert np.array_equal(f2[..., 0], rr) and np.array_equal(f2[..., 1], ri)
+    pw = rng.integers(0, 1 << 30, (40, 256)).astype(np.uint32)
+    assert np.array_equal(u16(m.filterbank(dev(pw.view(np.int32), np.int32))), R.filterbank(pw, ntap=32))
+    allm = np.arange(65536, dtype=np.uint16)
+    assert np.array_equal(u16(m.log2(dev(allm.view(np.int16)))), R.log2fix(allm))
+    L = rng.integers(0, 32768, (64, 32)).astype(np.int16)
+    assert np.array_equal(m.dct_stream(dev(L)).cpu().numpy(), R.dct_stream(L, 32))
+
+
+def test_stage_operators_16_filters(ops):
+    from oracle import ref_np as R
+    m = ops[(16, 16)]
+    rng = np.random.default_rng(4)
+    pw = rng.integers(0, 1 << 30, (40, 256)).astype(np.uint32)
+    assert np.array_equal(u16(m.filterbank(dev(pw.view(np.int32), np.int32))), R.filterbank(pw, ntap=16))
+    L = rng.integers(0, 32768, (64, 16)).astype(np.int16)
+    assert np.array_equal(m.dct_stream(dev(L)).cpu().numpy(), R.dct_stream(L, 16))
+
+
+# ---- streaming -----------------------------------------------------------------------
+def test_streaming_matches_batch(ops, RC):
+    m = ops[(32, 16)]
+    cfg = RC.RefConfig(nfilters=32, nceptrums=16)
+    rng = np.random.default_rng(9)
+    S, steps = 70, 12
+    hops = rng.integers(-30000, 30000, (S, steps, 170)).astype(np.int16)
+    m.reset(S)
+    outs = []
+    for t in range(steps):
+        outs.append(m.step(dev(hops[:, t])).cpu().numpy())
+    got = np.stack(outs, axis=1)
+    # zero state = 342 zeros already pushed after reset
+    x = np.concatenate([np.zeros((S, 342), np.int16), hops.reshape(S, -1)], axis=1)
+    want = RC.run(cfg, x, threads=4)
+    assert want.shape == got.shape and np.array_equal(got, want)
+
+
+def test_errors(ops):
+    import mfcc_b200
+    m = ops[(32, 32)]
+    with pytest.raises(TypeError):
+        m(torch.zeros(1000, device="cuda"))
+    with pytest.raises(ValueError):
+        m(torch.zeros(1000, dtype=torch.int16))
+    with pytest.raises(ValueError):
+        mfcc_b200.MFCC(nfft=256)
+    with pytest.raises(ValueError):
+        mfcc_b200.MFCC(nfilters=64, nceptrums=16)

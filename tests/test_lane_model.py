@@ -1,0 +1,51 @@
+"""CPU check of the kernel's design: tests/lane_model.py mirrors the CUDA warp
+algorithm (index maps, skews, per-lane twiddles, DCT shuffle plan); here it must
+reproduce the oracle bit for bit and its shared-memory accesses must be conflict free."""
+import math
+
+import numpy as np
+import pytest
+
+import lane_model as LM
+from mfcc_b200 import tables as T
+from oracle import ref_np as R
+
+
+def test_fft512_lanes_bit_exact_and_conflict_free():
+    rng = np.random.default_rng(3)
+    tw = T.twiddle_table(512).astype(np.int64)
+    frames = [rng.integers(-32768, 32768, 512), np.tile([-32768, 32767], 256),
+              np.full(512, -32768), rng.integers(-3000, 3000, 512)]
+    for w in frames:
+        re, im, conf = LM.fft512_frame(w, tw)
+        rr, ri = R.fft_stream(w[None, :])
+        assert np.array_equal(re, rr[0]) and np.array_equal(im, ri[0])
+        assert max(conf.values()) == 1, {k: v for k, v in conf.items() if v > 1}
+
+
+@pytest.mark.parametrize("nf", [16, 32])
+def test_epilogue_lanes(nf, wav):
+    _, tp = R.mfcc(wav[:5000], nfilters=nf, nceptrums=nf, taps=True)
+    pts = R.get_filter_points(0, 8000.0, nf, 512, sample_rate=16e3)
+    lo = int(math.log2(pts[-1] - pts[-3])) + 60 - 34
+    twd = T.twiddle_table(4 * nf).astype(np.int64)
+    for k in range(tp["power"].shape[0]):
+        mel = LM.mel_lanes(tp["power"][k], nf, lo_bit=lo)
+        assert np.array_equal(mel, tp["filter"][k])
+        lg = np.array([LM.log2_lane(m) for m in mel])
+        assert np.array_equal(lg, tp["log"][k])
+        assert np.array_equal(LM.dct_lanes(lg, nf, twd), tp["dct"][k])
+    rng = np.random.default_rng(nf)
+    L = rng.integers(0, 32768, (16, nf))
+    dd = R.dct_stream(L, nf)
+    for k in range(len(L)):
+        assert np.array_equal(LM.dct_lanes(L[k], nf, twd), dd[k])
+    tw_idx, own = LM.dct_plan(nf)
+    assert own.tolist() == list(range(nf))          # lane j ends up with bin j
+
+
+def test_log2_lane_all_values():
+    m = np.arange(65536)
+    want = R.log2fix(m[::17], 16, 15)
+    got = np.array([LM.log2_lane(v) for v in m[::17]])
+    assert np.array_equal(got, want)
