@@ -142,7 +142,7 @@ def run_reference(args, rank, world):
     import numpy as np
     import torch
     threads = RC.max_threads()
-    n_clips = max(threads, 8)
+    n_clips = min(128, 4 * threads)
     cfg = RC.RefConfig(nfilters=NFILT, nceptrums=NCEP)
     x = synth_clips(n_clips, N_SAMPLES, torch.device("cpu")).numpy()
     frames = n_clips * cfg.num_frames(N_SAMPLES)
@@ -278,7 +278,7 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             from oracle import ref_c as RC
             thr = RC.max_threads()
-            ncl = max(thr, 8)
+            ncl = min(256, 16 * thr)        # ~20 core-seconds of CPU work
             v, fr, dt = cpu_oracle_rate(ncl, thr)
             line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": thr, "kind": "port",
                                     "sample": "%d clips x 60 s (%d frames), %.1f s" % (ncl, fr, dt)}
