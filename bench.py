@@ -74,7 +74,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "200"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -86,6 +86,11 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
+    def mark(self):
+        """Rows from here on belong to the timed region (nvidia-smi is started earlier:
+        its start-up stalls the driver for ~100 ms and must not fall inside it)."""
+        self.first = len(self.rows)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
@@ -95,7 +100,8 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
-        for r in self.rows:
+        rows = self.rows[getattr(self, "first", 0):] or self.rows
+        for r in rows:
             p = [s.strip() for s in r.split(",")]
             if len(p) < 8:
                 continue
@@ -205,10 +211,12 @@ def main():
     out = torch.empty((args.clips, K, NCEP), dtype=torch.int16, device=dev)
     frames_rank = args.clips * K
 
+    sampler = ClockSampler(local).start()
     for _ in range(args.warmup):
         op(x, out=out)
     barrier()
-    sampler = ClockSampler(local).start()
+    time.sleep(0.3)
+    sampler.mark()
     l0 = _lib.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     ev[0].record()
