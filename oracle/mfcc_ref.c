@@ -11,7 +11,9 @@
  * are built by oracle/ref_np.py the way the reference builds them at elaboration
  * time; this file holds only run-time arithmetic.
  *
- * Pinning: see the header of oracle/ref_np.py and DESIGN.md ("Oracle").
+ * Pinning: checked bit for bit, stage by stage, against vectors made by executing the
+ * reference's own RTL source (tests/golden/rtl_*.npz, tests/test_rtl_golden.py);
+ * see the header of oracle/ref_np.py and DESIGN.md ("Oracle and pinning").
  *
  * Build: make -C oracle      (gcc -O2 -fopenmp -shared -fPIC)
  */

@@ -1,0 +1,184 @@
+"""Parity against vectors produced by EXECUTING the reference's own RTL source
+(tests/golden/make_rtl_golden.py: /root/reference/mfcc/core/*.py run under
+oracle/hdl_shim).  The CPU tests pin both oracles (numpy and C) stage by stage; the GPU
+tests pin the CUDA path the same way, through the C-ABI."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ref_np as R
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+CASES = sorted(os.path.basename(p)[4:-4] for p in glob.glob(os.path.join(GOLD, "rtl_*.npz"))
+               if not p.endswith("rtl_stage_vectors.npz"))
+
+
+def load(case):
+    return np.load(os.path.join(GOLD, "rtl_%s.npz" % case))
+
+
+def s16(v):
+    return ((np.asarray(v, dtype=np.int64) + 32768) % 65536) - 32768
+
+
+def test_fixture_set_is_complete():
+    assert len(CASES) >= 14, CASES
+    assert os.path.exists(os.path.join(GOLD, "rtl_stage_vectors.npz"))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_numpy_oracle_matches_rtl_every_stage(case):
+    g = load(case)
+    nf, nc = int(g["nfilters"]), int(g["nceptrums"])
+    K = g["out"].shape[0]
+    out, t = R.mfcc(g["samples"], nfilters=nf, nceptrums=nc, n_frames=K, taps=True)
+    assert np.array_equal(t["frame"], s16(g["frame"]))
+    assert np.array_equal(t["window"], s16(g["window"]))
+    assert np.array_equal(t["fft_r"], s16(g["fft_r"]))
+    assert np.array_equal(t["fft_i"], s16(g["fft_i"]))
+    assert np.array_equal(t["power"], g["power"].astype(np.int64) & 0x3fffffff)
+    assert np.array_equal(t["filter"], g["filter"].astype(np.int64) & 0xffff)
+    assert np.array_equal(t["log"], g["log"])
+    assert np.array_equal(t["dct"], s16(g["dct"]))
+    assert np.array_equal(out, s16(g["out"]))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_c_oracle_matches_rtl_every_stage(case):
+    from oracle import ref_c as RC
+    RC.build()
+    g = load(case)
+    nf, nc = int(g["nfilters"]), int(g["nceptrums"])
+    K = g["out"].shape[0]
+    out, t = RC.run(RC.RefConfig(nfilters=nf, nceptrums=nc), g["samples"], n_frames=K, taps=True)
+    assert np.array_equal(t["window"], s16(g["window"]))
+    assert np.array_equal(t["fft"][..., 0], s16(g["fft_r"]))
+    assert np.array_equal(t["fft"][..., 1], s16(g["fft_i"]))
+    assert np.array_equal(t["power"], g["power"].astype(np.uint32))
+    assert np.array_equal(t["mel"], g["filter"].astype(np.uint16))
+    assert np.array_equal(t["log2"], g["log"].astype(np.uint16))
+    assert np.array_equal(t["dct"], s16(g["dct"]))
+    assert np.array_equal(out, s16(g["out"]))
+
+
+def test_stalled_run_equals_free_run():
+    """Back-pressure in the RTL bench must not change any value: the fixture made with
+    random stalls on both ends equals the oracle just like the free-running ones, and
+    its inputs overlap wav_mid_16c's, whose common frames must agree."""
+    a, b = load("wav_stalled"), load("wav_mid_16c")
+    n = min(a["dct"].shape[0], b["dct"].shape[0])
+    assert np.array_equal(a["dct"][:n], b["dct"][:n])
+    assert np.array_equal(a["filter"][:n], b["filter"][:n])
+
+
+def test_golden_covers_the_hard_cases():
+    """The fixtures must exercise what makes the path intricate: the 16-bit mel wrap
+    (SURVEY.md F7), log2(0), FFT 16-bit wraps and the zero-padded tail."""
+    g = load("noise_full")
+    # mel values whose unwrapped register exceeds 16 bits exist for full-scale noise
+    pw = g["power"].astype(np.int64)
+    wide = R.filterbank(pw, 30, 24, 10, 16e3, 512, 32)        # same first bit, 8 more kept
+    assert (wide >= 65536).any() and np.array_equal(wide & 0xffff, g["filter"])
+    assert (load("zeros")["filter"] == 0).all() and (load("zeros")["log"] == 0).all()
+    assert load("short_padded")["samples"].size < 512 + 170 * 3
+    alt = load("alt_fullscale")
+    assert np.abs(alt["fft_r"]).max() > 0
+
+
+# ------------------------------------------------------------------ single stages
+@pytest.fixture(scope="module")
+def sv():
+    return np.load(os.path.join(GOLD, "rtl_stage_vectors.npz"))
+
+
+def test_stage_fft_core_and_stream(sv):
+    x = sv["fft512_in"]
+    re, im = R.fft_int(x, np.zeros_like(x), 512)
+    assert np.array_equal(re[:256], sv["fft512_out"][:, 0])
+    assert np.array_equal(im[:256], sv["fft512_out"][:, 1])
+    re, im = R.fft_stream(sv["fftstream_in"], 512)
+    assert np.array_equal(re, sv["fftstream_out"][:, :, 0])
+    assert np.array_equal(im, sv["fftstream_out"][:, :, 1])
+
+
+def test_stage_dct(sv):
+    assert np.array_equal(R.dct_stream(sv["dct16_in"], 16), s16(sv["dct16_out"]))
+    assert np.array_equal(R.dct_stream(sv["dct32_in"], 32), s16(sv["dct32_out"]))
+    assert np.array_equal(R.dct_stream(sv["dct32s_in"], 32), s16(sv["dct32s_out"]))
+
+
+def test_stage_log2(sv):
+    assert np.array_equal(R.log2fix(sv["log2_in"], 16, 15), sv["log2_out"])
+
+
+def test_stage_power(sv):
+    p = sv["power_in"]
+    assert np.array_equal(R.power_spectrum(p[:, 0], p[:, 1], 16, 30), sv["power_out"])
+
+
+@pytest.mark.parametrize("ntap", [16, 32])
+def test_stage_filterbank(sv, ntap):
+    got = R.filterbank(sv["mel%d_in" % ntap], 30, 16, 18, 16e3, 512, ntap)
+    assert np.array_equal(got, sv["mel%d_out" % ntap])
+    # the all-ones row overflows the 16 kept bits on the wide filters: the wrap is real
+    assert (sv["mel%d_out" % ntap] < 65536).all()
+
+
+def test_stage_window(sv):
+    assert np.array_equal(R.window(sv["window_in"], 512, 8), sv["window_out"])
+
+
+# ------------------------------------------------------------------ CUDA path
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES)
+def test_cuda_matches_rtl_every_stage(case):
+    import torch
+    import mfcc_b200
+    g = load(case)
+    nf, nc = int(g["nfilters"]), int(g["nceptrums"])
+    K = g["out"].shape[0]
+    op = mfcc_b200.MFCC(nfilters=nf, nceptrums=nc, device="cuda:0")
+    x = torch.from_numpy(np.ascontiguousarray(g["samples"])).to("cuda:0")
+    out, t = op(x, n_frames=K, taps=True)
+    torch.cuda.synchronize()
+    u16 = lambda a: a.cpu().numpy().view(np.uint16).astype(np.int64)
+    assert np.array_equal(t["window"].cpu().numpy(), s16(g["window"]))
+    assert np.array_equal(t["fft"].cpu().numpy()[..., 0], s16(g["fft_r"]))
+    assert np.array_equal(t["fft"].cpu().numpy()[..., 1], s16(g["fft_i"]))
+    assert np.array_equal(t["power"].cpu().numpy().view(np.uint32), g["power"].astype(np.uint32))
+    assert np.array_equal(u16(t["filter"]), g["filter"])
+    assert np.array_equal(u16(t["log"]), g["log"])
+    assert np.array_equal(t["dct"].cpu().numpy(), s16(g["dct"]))
+    assert np.array_equal(out.cpu().numpy(), s16(g["out"]))
+    # the production instantiation (no taps, batched with a copy of itself)
+    out2 = op(torch.stack([x, x]), n_frames=K)
+    assert np.array_equal(out2[1].cpu().numpy(), s16(g["out"]))
+
+
+@pytest.mark.gpu
+def test_cuda_stage_operators_match_rtl_stage_vectors(sv):
+    import torch
+    import mfcc_b200 as M
+    dev = "cuda:0"
+    T = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a).astype(dt)).to(dev)
+    got = M.FftStream(16, 512, device=dev)(T(sv["fftstream_in"], np.int16)).cpu().numpy()
+    assert np.array_equal(got, sv["fftstream_out"])
+    got = M.WindowHamming(16, 512, 8, device=dev)(T(sv["window_in"], np.int16)).cpu().numpy()
+    assert np.array_equal(got, sv["window_out"])
+    got = M.Log2Fix(16, 15, device=dev)(T(sv["log2_in"].astype(np.uint16).view(np.int16), np.int16))
+    assert np.array_equal(got.cpu().numpy().view(np.uint16), sv["log2_out"])
+    for ntap in (16, 32):
+        fb = M.FilterBank(30, 16, None, 18, 16e3, 512, ntap, device=dev)
+        got = fb(T(sv["mel%d_in" % ntap], np.int32)).cpu().numpy().view(np.uint16)
+        assert np.array_equal(got, sv["mel%d_out" % ntap])
+    d = M.DCTStream(16, 32, device=dev)
+    got = d(T(sv["dct32_in"].astype(np.uint16).view(np.int16), np.int16)).cpu().numpy()
+    assert np.array_equal(got, s16(sv["dct32_out"]))
+    got = M.DCTStream(16, 16, device=dev)(T(sv["dct16_in"].astype(np.uint16).view(np.int16), np.int16))
+    assert np.array_equal(got.cpu().numpy(), s16(sv["dct16_out"]))
+    p = sv["power_in"]
+    got = M.PowerSpectrum(16, 30, device=dev)(T(p[None], np.int16)).cpu().numpy().view(np.uint32)
+    assert np.array_equal(got[0], sv["power_out"])
