@@ -30,6 +30,7 @@ class MFCCConfig:
     mel_gain: int = 18              # FilterBank(gain=18)
     log_width_out: int = 15         # Log2Fix(filterbank.width_output, 15)  :82
     mode: int = MODE_INT
+    mel_floor: float = 0.0          # fp32 mode: mel energies are clamped to this before log2 (0 = off)
 
     def __post_init__(self):
         if self.width != 16:
@@ -44,6 +45,8 @@ class MFCCConfig:
             raise ValueError("nceptrums must be in 1..nfilters")
         if self.mode not in (MODE_INT, MODE_FP32):
             raise ValueError("mode must be MODE_INT or MODE_FP32")
+        if not self.mel_floor >= 0.0:
+            raise ValueError("mel_floor must be >= 0")
 
     @property
     def hop(self) -> int:

@@ -1,0 +1,186 @@
+// Device-side building blocks of the fp32 mode of the B200 MFCC path.
+//
+// Same chain as the integer mode, in float32, following the reference's float
+// prototype notebook/MFCC-INT.ipynb cells 2-10 (pre-emphasis 0.96875, periodic Hamming,
+// fft/512 with 257 bins, |X|^2, dense triangular mel filters, log2, orthonormal DCT-II).
+//
+// One warp = one frame.  The 512 real samples are packed into 256 complex values and
+// transformed as 8 x 8 x 4: two radix-8 passes inside the lanes with one transpose
+// through shared memory, a radix-4 pass across groups of four lanes by shuffles, then
+// the split of the packed spectrum into bins 0..256 fused with the power spectrum.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mfccf {
+
+constexpr int NFFT = 512;
+constexpr int HOP = 170;
+constexpr int NBINS1 = 257;            // the notebook keeps bins 0..256 (cell 5)
+constexpr int MELW_MAX = 608;          // sum of the filter spans (2 * 257 plus slack)
+constexpr int XWF = 848;               // 32-bit words of the per-warp exchange buffer
+constexpr int T1_STRIDE = 36;          // float2 per row of the first transpose
+constexpr int PW_OFF = 576;            // power spectrum lives behind the transpose area
+constexpr unsigned FULL = 0xffffffffu;
+
+struct alignas(16) DevTablesF {
+    float  window[NFFT];               // hamming(512, periodic) / 32: see load_z()
+    float2 tw256[256];                 // exp(-2 pi i k / 256)
+    float2 tw512[132];                 // exp(-2 pi i k / 512), k = 0..128
+    float  dct[32 * 32];               // dct[n * 32 + k] = D[k][n] (orthonormal DCT-II)
+    float  melw[MELW_MAX];             // the non-zero span of every filter, concatenated
+    int16_t mel_lo[32];                // first bin of filter m's span
+    int16_t mel_n[32];                 // bins in the span
+    int16_t mel_off[32];               // offset of the span in melw[]
+    float  mel_floor;                  // energies are clamped to this before log2 (0 = off)
+    int32_t pad[3];
+};
+static_assert(sizeof(DevTablesF) % 16 == 0, "DevTablesF must be int4-copyable");
+
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cmul(float2 a, float2 w) {
+    return make_float2(fmaf(a.x, w.x, -a.y * w.y), fmaf(a.x, w.y, a.y * w.x));
+}
+__device__ __forceinline__ float2 mul_mj(float2 a) { return make_float2(a.y, -a.x); }    // * (-j)
+
+// 8-point forward DFT in registers (decimation in frequency); on return v[j] holds
+// bin brev3(j).
+__device__ __forceinline__ void fft8(float2 (&v)[8])
+{
+    constexpr float S = 0.70710678118654752f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 a = cadd(v[i], v[i + 4]), b = csub(v[i], v[i + 4]);
+        v[i] = a;
+        if (i == 0) v[4] = b;
+        else if (i == 1) v[5] = make_float2((b.x + b.y) * S, (b.y - b.x) * S);     // * W8^1
+        else if (i == 2) v[6] = mul_mj(b);                                         // * W8^2
+        else v[7] = make_float2((b.y - b.x) * S, -(b.x + b.y) * S);                // * W8^3
+    }
+#pragma unroll
+    for (int h = 0; h < 8; h += 4) {
+        const float2 a0 = cadd(v[h], v[h + 2]), b0 = csub(v[h], v[h + 2]);
+        const float2 a1 = cadd(v[h + 1], v[h + 3]), b1 = mul_mj(csub(v[h + 1], v[h + 3]));
+        v[h] = a0; v[h + 1] = a1; v[h + 2] = b0; v[h + 3] = b1;
+    }
+#pragma unroll
+    for (int h = 0; h < 8; h += 2) {
+        const float2 a = cadd(v[h], v[h + 1]), b = csub(v[h], v[h + 1]);
+        v[h] = a; v[h + 1] = b;
+    }
+}
+__host__ __device__ constexpr int brev3(int v) { return ((v & 1) << 2) | (v & 2) | ((v & 4) >> 2); }
+
+// Pre-emphasis + window for the two samples of one 32-bit word (samples 2n, 2n+1).
+//   y = x - 0.96875 * xp = (32 x - 31 xp) / 32 is an exact integer / 32 (|.| < 2^21), so
+// it is formed in integer arithmetic and turned into a float by the 1.5 * 2^23 bias
+// trick (no I2F); the 1/32 is folded into the window table.
+__device__ __forceinline__ float2 emph_win(unsigned w, unsigned wprev, float w0, float w1)
+{
+    const int x0 = (int)(short)(w & 0xffffu), x1 = (int)w >> 16, xp = (int)wprev >> 16;
+    constexpr int MAGIC = 0x4B400000;                      // 1.5 * 2^23 = 12582912.0f
+    const float f0 = __int_as_float(MAGIC + (32 * x0 - 31 * xp)) - 12582912.0f;
+    const float f1 = __int_as_float(MAGIC + (32 * x1 - 31 * x0)) - 12582912.0f;
+    return make_float2(f0 * w0, f1 * w1);
+}
+
+// index of packed-spectrum bin k in the exchange buffer (4 float2 of padding per 64)
+__device__ __forceinline__ int zaddr(int k) { return k + ((k >> 6) << 2); }
+
+// ---------------------------------------------------------------------------------
+// Power spectrum |X[b]|^2 / 512^2, b = 0..256, of one frame into pw[] (shared memory).
+//   raw: the frame's int16 samples in shared memory (even halfword offset), raw[-1] is
+//        the sample before the frame (0 at the start of a stream)
+__device__ __forceinline__ void power_warp_f32(const int16_t *raw, float *xb, const DevTablesF *tab, int lane)
+{
+    float2 *xc = reinterpret_cast<float2 *>(xb);
+    float *pw = xb + PW_OFF;
+    const unsigned *r32 = reinterpret_cast<const unsigned *>(raw);
+    const float2 *win2 = reinterpret_cast<const float2 *>(tab->window);
+    // ---- z[n] = (y[2n] w[2n], y[2n+1] w[2n+1]), n = lane + 32 a
+    float2 v[8];
+#pragma unroll
+    for (int a = 0; a < 8; ++a) {
+        const int n = lane + 32 * a;
+        const float2 ww = win2[n];
+        v[a] = emph_win(r32[n], r32[n - 1], ww.x, ww.y);
+    }
+    // ---- pass 1: DFT-8 over a, twiddle W256^(lane * k1), transpose
+    fft8(v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int k1 = brev3(j);
+        float2 y = v[j];
+        if (k1) y = cmul(y, tab->tw256[lane * k1]);
+        xc[k1 * T1_STRIDE + lane] = y;
+    }
+    __syncwarp();
+    // lane = (k1, c): the 8 values l = c + 4 b of row k1
+    const int k1 = lane >> 2, c = lane & 3;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) v[b] = xc[k1 * T1_STRIDE + c + 4 * b];
+    __syncwarp();
+    // ---- pass 2: DFT-8 over b, twiddle W32^(c p) = W256^(8 c p)
+    fft8(v);
+    // ---- pass 3: DFT-4 over c across the four lanes of a group; lane c ends with
+    //      q = {0, 2, 1, 3}[c] of Z[k1 + 8 p + 64 q]
+    const float sg = (c & 2) ? -1.0f : 1.0f, sg1 = (c & 1) ? -1.0f : 1.0f;
+    const int q = ((c & 1) << 1) | (c >> 1);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int p = brev3(j);
+        float2 y = v[j];
+        if (p) y = cmul(y, tab->tw256[8 * c * p]);
+        float2 o;
+        o.x = __shfl_xor_sync(FULL, y.x, 2);
+        o.y = __shfl_xor_sync(FULL, y.y, 2);
+        y = make_float2(fmaf(sg, y.x, o.x), fmaf(sg, y.y, o.y));     // c<2: mine+other, else other-mine
+        if (c == 3) y = mul_mj(y);
+        o.x = __shfl_xor_sync(FULL, y.x, 1);
+        o.y = __shfl_xor_sync(FULL, y.y, 1);
+        y = make_float2(fmaf(sg1, y.x, o.x), fmaf(sg1, y.y, o.y));
+        xc[zaddr(k1 + 8 * p + 64 * q)] = y;
+    }
+    __syncwarp();
+    // ---- split: X[k] = F + W512^k G, X[256-k] = conj(F - W512^k G), with
+    //      F = (Z[k] + conj Z[256-k]) / 2, G = (Z[k] - conj Z[256-k]) / 2j
+    constexpr float SC = 1.0f / (512.0f * 512.0f);          // fft / 512 (cell 5), squared
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int k = lane + 32 * i;
+        const float2 A = xc[zaddr(k)];
+        const float2 B = xc[zaddr((256 - k) & 255)];
+        const float2 w = tab->tw512[k];
+        const float2 F = make_float2(0.5f * (A.x + B.x), 0.5f * (A.y - B.y));
+        const float2 G = make_float2(0.5f * (A.y + B.y), -0.5f * (A.x - B.x));
+        const float2 T = cmul(G, w);
+        const float2 X0 = cadd(F, T), X1 = csub(F, T);
+        pw[k] = (X0.x * X0.x + X0.y * X0.y) * SC;
+        pw[256 - k] = (X1.x * X1.x + X1.y * X1.y) * SC;      // k = 0 gives bin 256
+    }
+    if (lane == 0) {                                         // bin 128: W512^128 = -j
+        const float2 A = xc[zaddr(128)];
+        pw[128] = (A.x * A.x + A.y * A.y) * SC;
+    }
+    __syncwarp();
+}
+
+// mel -> log2 -> DCT-II of the power spectrum in pw[]; lane k returns coefficient k.
+template <int NF>
+__device__ __forceinline__ float cepstrum_warp_f32(const float *pw, const DevTablesF *tab, int lane)
+{
+    const int m = lane & (NF - 1);
+    const int lo = tab->mel_lo[m], n = tab->mel_n[m];
+    const float *w = tab->melw + tab->mel_off[m];
+    float acc = 0.0f;
+    for (int j = 0; j < n; ++j) acc = fmaf(w[j], pw[lo + j], acc);
+    const float L = __log2f(fmaxf(acc, tab->mel_floor));
+    float out = 0.0f;
+#pragma unroll
+    for (int nn = 0; nn < NF; ++nn)
+        out = fmaf(__shfl_sync(FULL, L, nn), tab->dct[nn * 32 + m], out);
+    return out;
+}
+
+}  // namespace mfccf

@@ -17,6 +17,7 @@
 
 #include "../../include/mfcc_b200.h"
 #include "mfcc_dev.cuh"
+#include "mfcc_f32.cuh"
 
 using namespace mfccb;
 
@@ -31,9 +32,10 @@ constexpr int CTAS_PER_SM = 4;
 struct RunParams {
     const int16_t *x;
     long long clip_stride, n_samples, n_frames;
-    int16_t *out;
+    void *out;            // int16 (integer mode) or float (fp32 mode)
     long long out_clip_stride;
     const DevTables *tab;
+    const mfccf::DevTablesF *ftab;
     long long n_tiles;
     int tiles_per_clip;
     int nceptrums;
@@ -207,11 +209,78 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
             if (tid == 0 && nxt < p.n_tiles) issue_tile(p, nxt, sm);
         }
         const int off0 = (int)(HOP * g.f0 - g.a0);          // even, 8..14
-        int16_t *orow = p.out + g.ci * p.out_clip_stride;
+        int16_t *orow = static_cast<int16_t *>(p.out) + g.ci * p.out_clip_stride;
         for (int fl = warp; fl < g.nf; fl += WARPS) {
             const long long k = g.f0 + fl;
             frame_warp<NF>(sm->pre + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
                            orow + k * p.nceptrums, p.nceptrums, p.taps, k);
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ fp32 fused kernel
+// Same tiling as mfcc_int_fused.  There is no shared pre-emphasis pass (each lane forms
+// y = x - 0.96875 xp for its own samples), so the raw tile is read during the compute
+// phase and is double buffered: the bulk copy of tile i+1 is issued before tile i is
+// computed.
+struct SmemF {
+    mfccf::DevTablesF tab;
+    alignas(16) int16_t raw[2][RAWN];
+    alignas(16) float xbuf[WARPS][mfccf::XWF];
+    alignas(8) uint64_t mbar[2];
+};
+
+__device__ __forceinline__ void issue_tile_f(const RunParams &p, long long t, SmemF *sm, int buf) {
+    const Tile g = tile_geo(p, t);
+    const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
+    if (bytes) {
+        mbar_arrive_expect_tx(&sm->mbar[buf], bytes);
+        tma_load_1d(sm->raw[buf] + g.lo, g.clip + g.a0 + g.lo, bytes, &sm->mbar[buf]);
+    } else {
+        mbar_arrive(&sm->mbar[buf]);
+    }
+}
+
+template <int NF>
+__global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    SmemF *sm = reinterpret_cast<SmemF *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const int4 *src = reinterpret_cast<const int4 *>(p.ftab);
+        int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
+        for (int i = tid; i < (int)(sizeof(mfccf::DevTablesF) / 16); i += THREADS) dst[i] = src[i];
+    }
+    if (tid == 0) { mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1); }
+    __syncthreads();
+
+    long long tile = blockIdx.x;
+    if (tid == 0 && tile < p.n_tiles) issue_tile_f(p, tile, sm, 0);
+    for (int it = 0; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const Tile g = tile_geo(p, tile);
+        int16_t *raw = sm->raw[buf];
+        for (int j = tid; j < g.lo; j += THREADS) raw[j] = 0;
+        for (int j = g.hi + tid; j < g.len; j += THREADS) {
+            const long long s = g.a0 + j;
+            raw[j] = (s >= 0 && s < p.n_samples) ? g.clip[s] : (int16_t)0;
+        }
+        {   // the other buffer was released by the barrier that ended the previous tile
+            const long long nxt = tile + gridDim.x;
+            if (tid == 0 && nxt < p.n_tiles) issue_tile_f(p, nxt, sm, buf ^ 1);
+        }
+        mbar_wait(&sm->mbar[buf], (uint32_t)(it >> 1) & 1u);
+        __syncthreads();
+        const int off0 = (int)(HOP * g.f0 - g.a0);          // even, 8..14
+        float *orow = static_cast<float *>(p.out) + g.ci * p.out_clip_stride;
+        for (int fl = warp; fl < g.nf; fl += WARPS) {
+            const long long k = g.f0 + fl;
+            mfccf::power_warp_f32(raw + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane);
+            const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, &sm->tab, lane);
+            if (lane < p.nceptrums) orow[k * p.nceptrums + lane] = c;
+            __syncwarp();
         }
         __syncthreads();
     }
@@ -296,8 +365,10 @@ __global__ void __launch_bounds__(THREADS) k_warp_stage(const void *in, void *ou
             __syncwarp();
             if (lane < NF) reinterpret_cast<uint16_t *>(out)[k * NF + lane] = (uint16_t)mel;
         } else {
-            const uint16_t *lg = reinterpret_cast<const uint16_t *>(in) + k * NF;
-            const unsigned L = lg[lane & (NF - 1)];
+            // DCTStream's sink is signed 16 bits (dct_stream.py:11); the chain only ever
+            // feeds it 15-bit log values, the stage operator may be given any int16
+            const int16_t *lg = reinterpret_cast<const int16_t *>(in) + k * NF;
+            const unsigned L = (unsigned)(int)lg[lane & (NF - 1)];
             const int c = dct_warp<NF>(L, &sm->tab, lane);
             if (lane < NF) reinterpret_cast<int16_t *>(out)[k * NF + lane] = (int16_t)c;
         }
@@ -360,6 +431,46 @@ __global__ void __launch_bounds__(THREADS) mfcc_int_step(int16_t *state, const i
     }
 }
 
+// fp32 streaming step: same state layout as the integer mode (raw samples).
+struct StepSmemF {
+    mfccf::DevTablesF tab;
+    alignas(16) int16_t raw[WARPS][NFFT + 8];   // raw[w][1] = sample before the frame, frame from [2]
+    alignas(16) float xbuf[WARPS][mfccf::XWF];
+};
+
+template <int NF>
+__global__ void __launch_bounds__(THREADS) mfcc_f32_step(int16_t *state, const int16_t *hop, int n_streams,
+                                                         float *out, int nceptrums, const mfccf::DevTablesF *gtab)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    StepSmemF *sm = reinterpret_cast<StepSmemF *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const int4 *src = reinterpret_cast<const int4 *>(gtab);
+        int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
+        for (int i = tid; i < (int)(sizeof(mfccf::DevTablesF) / 16); i += THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    constexpr int HIST = NFFT - HOP;                      // 342
+    for (int s = blockIdx.x * WARPS + warp; s < n_streams; s += gridDim.x * WARPS) {
+        int16_t *st = state + (long long)s * STATE_N;     // st[0] = prev, st[1..342] = history
+        const int16_t *hp = hop + (long long)s * HOP;
+        int16_t *raw = sm->raw[warp];
+        // raw(n) for n = -1 .. 511 at raw[2 + n]
+        for (int i = lane; i <= NFFT; i += 32) {
+            const int n = i - 1;
+            raw[2 + n] = (n < HIST) ? st[1 + n] : hp[n - HIST];
+        }
+        __syncwarp();
+        // new state = raw(HOP-1 .. 511)
+        for (int i = lane; i <= HIST; i += 32) st[i] = raw[2 + i + HOP - 1];
+        mfccf::power_warp_f32(raw + 2, sm->xbuf[warp], &sm->tab, lane);
+        const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, &sm->tab, lane);
+        if (lane < nceptrums) out[(long long)s * nceptrums + lane] = c;
+        __syncwarp();
+    }
+}
+
 // ------------------------------------------------------------------ host side
 thread_local std::string g_err;
 std::atomic<long long> g_launches{0};
@@ -375,12 +486,13 @@ int fail(int code, const std::string &msg) { g_err = msg; return code; }
 struct Handle {
     mfcc_b200_cfg cfg;
     DevTables *d_tab = nullptr;
+    mfccf::DevTablesF *d_ftab = nullptr;
     int device = 0;
     int sm_count = 0;
     // staging for mfcc_b200_run_host
     cudaStream_t st[2] = {nullptr, nullptr};
     int16_t *d_in[2] = {nullptr, nullptr};
-    int16_t *d_out[2] = {nullptr, nullptr};
+    void *d_out[2] = {nullptr, nullptr};
     size_t in_cap = 0, out_cap = 0;
 };
 
@@ -455,6 +567,33 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
     return MFCC_B200_OK;
 }
 
+int build_tables_f(const mfcc_b200_cfg &c, mfccf::DevTablesF &t) {
+    memset(&t, 0, sizeof(t));
+    const double PI = 3.14159265358979323846;
+    const int nf = c.nfilters;
+    for (int n = 0; n < NFFT; ++n) t.window[n] = c.f_window[n] * (1.0f / 32.0f);   // see emph_win()
+    for (int k = 0; k < 256; ++k)
+        t.tw256[k] = make_float2((float)cos(2 * PI * k / 256), (float)-sin(2 * PI * k / 256));
+    for (int k = 0; k <= 128; ++k)
+        t.tw512[k] = make_float2((float)cos(2 * PI * k / 512), (float)-sin(2 * PI * k / 512));
+    for (int k = 0; k < nf; ++k)
+        for (int n = 0; n < nf; ++n) t.dct[n * 32 + k] = c.f_dct[k * nf + n];
+    int off = 0;
+    for (int m = 0; m < nf; ++m) {
+        const float *row = c.f_mel + (size_t)m * mfccf::NBINS1;
+        int lo = 0, hi = mfccf::NBINS1;
+        while (lo < hi && row[lo] == 0.0f) ++lo;
+        while (hi > lo && row[hi - 1] == 0.0f) --hi;
+        if (off + (hi - lo) > mfccf::MELW_MAX)
+            return fail(MFCC_B200_EUNSUPPORTED, "f_mel is too dense for the sparse filter table");
+        t.mel_lo[m] = (int16_t)lo; t.mel_n[m] = (int16_t)(hi - lo); t.mel_off[m] = (int16_t)off;
+        for (int b = lo; b < hi; ++b) t.melw[off++] = row[b];
+    }
+    t.mel_floor = c.f_mel_floor > 0.0f ? c.f_mel_floor : 0.0f;
+    (void)c.f_preemph;
+    return MFCC_B200_OK;
+}
+
 template <typename K>
 int set_smem(K kernel, size_t bytes) {
     CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
@@ -487,7 +626,13 @@ int mfcc_b200_create(const mfcc_b200_cfg *cfg, void **handle)
     if (!cfg || !handle) return fail(MFCC_B200_EINVAL, "null argument");
     *handle = nullptr;
     if (cfg->struct_size != (int32_t)sizeof(mfcc_b200_cfg)) return fail(MFCC_B200_EINVAL, "mfcc_b200_cfg size mismatch");
-    if (cfg->mode != MFCC_B200_MODE_INT) return fail(MFCC_B200_EUNSUPPORTED, "only MFCC_B200_MODE_INT is built so far");
+    if (cfg->mode != MFCC_B200_MODE_INT && cfg->mode != MFCC_B200_MODE_FP32) return fail(MFCC_B200_EINVAL, "unknown mode");
+    if (cfg->mode == MFCC_B200_MODE_FP32) {
+        if (!cfg->f_window || !cfg->f_mel || !cfg->f_dct) return fail(MFCC_B200_EINVAL, "fp32 mode needs f_window, f_mel and f_dct");
+        if (cfg->f_preemph != 0.96875f)
+            return fail(MFCC_B200_EUNSUPPORTED, "the fp32 kernels cover f_preemph = 0.96875 (notebook/MFCC-INT.ipynb cell 2)");
+        if (!(cfg->f_mel_floor >= 0.0f)) return fail(MFCC_B200_EINVAL, "f_mel_floor must be >= 0");
+    }
     if (cfg->nfft != NFFT || cfg->hop != HOP) return fail(MFCC_B200_EUNSUPPORTED, "kernels cover nfft=512, hop=170");
     if (cfg->nfilters != 16 && cfg->nfilters != 32) return fail(MFCC_B200_EUNSUPPORTED, "kernels cover nfilters 16 and 32");
     if (cfg->nceptrums < 1 || cfg->nceptrums > cfg->nfilters) return fail(MFCC_B200_EINVAL, "nceptrums out of range");
@@ -505,12 +650,23 @@ int mfcc_b200_create(const mfcc_b200_cfg *cfg, void **handle)
     DevTables t;
     int rc = build_tables(*cfg, t);
     if (rc) { delete h; return rc; }
+    mfccf::DevTablesF *tf = nullptr;
+    if (cfg->mode == MFCC_B200_MODE_FP32) {
+        tf = new mfccf::DevTablesF();
+        rc = build_tables_f(*cfg, *tf);
+        if (rc) { delete tf; delete h; return rc; }
+    }
+    h->cfg.f_window = nullptr; h->cfg.f_mel = nullptr; h->cfg.f_dct = nullptr;
     cudaError_t e = cudaGetDevice(&h->device);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_tab, sizeof(DevTables));
     if (e == cudaSuccess) e = cudaMemcpy(h->d_tab, &t, sizeof(DevTables), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && tf) e = cudaMalloc(&h->d_ftab, sizeof(mfccf::DevTablesF));
+    if (e == cudaSuccess && tf) e = cudaMemcpy(h->d_ftab, tf, sizeof(mfccf::DevTablesF), cudaMemcpyHostToDevice);
+    delete tf;
     if (e != cudaSuccess) {
         if (h->d_tab) cudaFree(h->d_tab);
+        if (h->d_ftab) cudaFree(h->d_ftab);
         delete h;
         return fail(MFCC_B200_ECUDA, std::string("mfcc_b200_create: ") + cudaGetErrorString(e));
     }
@@ -523,7 +679,11 @@ int mfcc_b200_create(const mfcc_b200_cfg *cfg, void **handle)
     if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_MEL, 16>, sizeof(StageSmem));
     if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_DCT, 32>, sizeof(StageSmem));
     if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_DCT, 16>, sizeof(StageSmem));
-    if (rc) { cudaFree(h->d_tab); delete h; return rc; }
+    if (!rc) rc = set_smem(mfcc_f32_fused<32>, sizeof(SmemF));
+    if (!rc) rc = set_smem(mfcc_f32_fused<16>, sizeof(SmemF));
+    if (!rc) rc = set_smem(mfcc_f32_step<32>, sizeof(StepSmemF));
+    if (!rc) rc = set_smem(mfcc_f32_step<16>, sizeof(StepSmemF));
+    if (rc) { cudaFree(h->d_tab); if (h->d_ftab) cudaFree(h->d_ftab); delete h; return rc; }
     *handle = h;
     return MFCC_B200_OK;
 }
@@ -538,6 +698,7 @@ void mfcc_b200_destroy(void *handle)
         if (h->d_out[i]) cudaFree(h->d_out[i]);
     }
     if (h->d_tab) cudaFree(h->d_tab);
+    if (h->d_ftab) cudaFree(h->d_ftab);
     delete h;
 }
 
@@ -552,22 +713,29 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
     if (n_clips > 1 && (clip_stride < n_samples || out_clip_stride < n_frames * h->cfg.nceptrums))
         return fail(MFCC_B200_EINVAL, "row pitch smaller than the row");
     if (taps && n_clips != 1) return fail(MFCC_B200_EINVAL, "taps need n_clips == 1");
+    const bool f32 = h->cfg.mode == MFCC_B200_MODE_FP32;
+    if (taps && f32) return fail(MFCC_B200_EUNSUPPORTED, "taps are an integer-mode feature");
     if (HOP * (n_frames - 1) + NFFT > (1LL << 40)) return fail(MFCC_B200_EINVAL, "clip too long");
 
     RunParams p;
     memset(&p, 0, sizeof(p));
     p.x = d_x; p.clip_stride = clip_stride; p.n_samples = n_samples; p.n_frames = n_frames;
-    p.out = static_cast<int16_t *>(d_out); p.out_clip_stride = out_clip_stride;
-    p.tab = h->d_tab; p.nceptrums = h->cfg.nceptrums;
+    p.out = d_out; p.out_clip_stride = out_clip_stride;
+    p.tab = h->d_tab; p.ftab = h->d_ftab; p.nceptrums = h->cfg.nceptrums;
     p.tiles_per_clip = (int)((n_frames + FT - 1) / FT);
     p.n_tiles = (long long)p.tiles_per_clip * n_clips;
     p.aligned = ((reinterpret_cast<uintptr_t>(d_x) & 15) == 0) && (n_clips == 1 || (clip_stride % 8) == 0);
     if (taps) p.taps = *taps;
-    long long grid = (long long)h->sm_count * CTAS_PER_SM;
+    long long grid = (long long)h->sm_count * (f32 ? 3 : CTAS_PER_SM);
     if (grid > p.n_tiles) grid = p.n_tiles;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (h->cfg.nfilters == 32) mfcc_int_fused<32><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
-    else                       mfcc_int_fused<16><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+    if (f32) {
+        if (h->cfg.nfilters == 32) mfcc_f32_fused<32><<<(unsigned)grid, THREADS, sizeof(SmemF), s>>>(p);
+        else                       mfcc_f32_fused<16><<<(unsigned)grid, THREADS, sizeof(SmemF), s>>>(p);
+    } else {
+        if (h->cfg.nfilters == 32) mfcc_int_fused<32><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+        else                       mfcc_int_fused<16><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+    }
     g_launches.fetch_add(1);
     CUDA_TRY(cudaGetLastError());
     return MFCC_B200_OK;
@@ -591,12 +759,13 @@ int mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, in
     long long per = (32LL << 20) / (in_row * 2);
     if (per < 1) per = 1;
     if (per > n_clips) per = n_clips;
-    const size_t in_need = (size_t)per * in_row * 2, out_need = (size_t)per * out_row * 2;
+    const size_t esz = h->cfg.mode == MFCC_B200_MODE_FP32 ? sizeof(float) : sizeof(int16_t);   // output element
+    const size_t in_need = (size_t)per * in_row * 2, out_need = (size_t)per * out_row * esz;
     if (in_need > h->in_cap || out_need > h->out_cap) {
         for (int i = 0; i < 2; ++i) {
             if (h->d_in[i]) cudaFree(h->d_in[i]);
             if (h->d_out[i]) cudaFree(h->d_out[i]);
-            h->d_in[i] = h->d_out[i] = nullptr;
+            h->d_in[i] = nullptr; h->d_out[i] = nullptr;
         }
         h->in_cap = h->out_cap = 0;
         for (int i = 0; i < 2; ++i) {
@@ -606,7 +775,7 @@ int mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, in
         }
         h->in_cap = in_need; h->out_cap = out_need;
     }
-    int16_t *out16 = static_cast<int16_t *>(h_out);
+    unsigned char *out8 = static_cast<unsigned char *>(h_out);
     int slot = 0;
     for (long long done = 0; done < n_clips; slot ^= 1) {
         const long long n = (n_clips - done) < per ? (n_clips - done) : per;
@@ -618,8 +787,8 @@ int mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, in
         if (int rc = mfcc_b200_run(h, h->d_in[slot], in_row, n_samples, (int32_t)n, n_frames, h->d_out[slot], out_row,
                                    nullptr, s))
             return rc;
-        CUDA_TRY(cudaMemcpy2DAsync(out16 + done * out_clip_stride, (size_t)out_clip_stride * 2, h->d_out[slot],
-                                   (size_t)out_row * 2, (size_t)out_row * 2, (size_t)n, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaMemcpy2DAsync(out8 + (size_t)done * out_clip_stride * esz, (size_t)out_clip_stride * esz, h->d_out[slot],
+                                   (size_t)out_row * esz, (size_t)out_row * esz, (size_t)n, cudaMemcpyDeviceToHost, s));
         done += n;
     }
     CUDA_TRY(cudaStreamSynchronize(h->st[0]));
@@ -633,6 +802,7 @@ int mfcc_b200_stage(void *handle, int32_t stage, const void *d_in, void *d_out, 
     if (int rc = check_handle(handle)) return rc;
     Handle *h = static_cast<Handle *>(handle);
     if (stage < 0 || stage >= MFCC_B200_STAGE_COUNT) return fail(MFCC_B200_EINVAL, "unknown stage");
+    if (h->cfg.mode != MFCC_B200_MODE_INT) return fail(MFCC_B200_EUNSUPPORTED, "stage operators are an integer-mode feature");
     if (n < 0 || n_frames < 0) return fail(MFCC_B200_EINVAL, "negative size");
     const long long rows = (stage == MFCC_B200_STAGE_FRAME) ? n_frames : n;
     if (rows == 0) return MFCC_B200_OK;
@@ -694,7 +864,14 @@ int mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n_
     const int cap = h->sm_count * 8;
     if (grid > cap) grid = cap;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (h->cfg.nfilters == 32)
+    if (h->cfg.mode == MFCC_B200_MODE_FP32) {
+        if (h->cfg.nfilters == 32)
+            mfcc_f32_step<32><<<grid, THREADS, sizeof(StepSmemF), s>>>((int16_t *)d_state, d_hop, n_streams, (float *)d_out,
+                                                                        h->cfg.nceptrums, h->d_ftab);
+        else
+            mfcc_f32_step<16><<<grid, THREADS, sizeof(StepSmemF), s>>>((int16_t *)d_state, d_hop, n_streams, (float *)d_out,
+                                                                        h->cfg.nceptrums, h->d_ftab);
+    } else if (h->cfg.nfilters == 32)
         mfcc_int_step<32><<<grid, THREADS, sizeof(StepSmem), s>>>((int16_t *)d_state, d_hop, n_streams, (int16_t *)d_out,
                                                                    h->cfg.nceptrums, h->d_tab);
     else

@@ -7,7 +7,7 @@ import math
 import numpy as np
 
 from . import _lib, tables
-from .config import MFCCConfig
+from .config import MFCCConfig, MODE_FP32
 
 
 class Handle:
@@ -50,6 +50,15 @@ class Handle:
         c.mel_weight = k["mel_w"].ctypes.data
         c.mel_close = k["mel_close"].ctypes.data
         c.f_preemph = 0.96875
+        if cfg.mode == MODE_FP32:
+            k["f_window"] = np.ascontiguousarray(tables.f_window(cfg.nfft), dtype=np.float32)
+            k["f_mel"] = np.ascontiguousarray(
+                tables.f_mel_filters(cfg.nfilters, cfg.nfft, cfg.samplerate), dtype=np.float32)
+            k["f_dct"] = np.ascontiguousarray(tables.f_dct_matrix(cfg.nfilters), dtype=np.float32)
+            c.f_window = k["f_window"].ctypes.data
+            c.f_mel = k["f_mel"].ctypes.data
+            c.f_dct = k["f_dct"].ctypes.data
+            c.f_mel_floor = float(cfg.mel_floor)
         self._c = c
         h = C.c_void_p()
         _lib.check(L.mfcc_b200_create(C.byref(c), C.byref(h)))

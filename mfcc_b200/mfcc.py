@@ -15,7 +15,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from .config import MFCCConfig, MODE_INT
+from .config import MFCCConfig, MODE_INT, MODE_FP32
 from .handle import Handle
 
 
@@ -38,11 +38,17 @@ def _check_samples(x, device):
 
 class MFCC:
     def __init__(self, width=16, nfft=512, samplerate=16e3, nfilters=16, nceptrums=16,
-                 mode="int", device=None):
-        if mode not in ("int",):
-            raise ValueError("mode must be 'int' (fp32 is not built yet)")
+                 mode="int", device=None, mel_floor=0.0):
+        if mode not in ("int", "fp32"):
+            raise ValueError("mode must be 'int' or 'fp32'")
+        self.mode = mode
+        # int: the FPGA's fixed point, bit exact.  fp32: the float prototype of
+        # notebook/MFCC-INT.ipynb cells 2-10, float32 cepstra; mel_floor > 0 clamps the
+        # mel energies before log2 (the notebook has none: silence gives -inf)
+        self.out_dtype = torch.int16 if mode == "int" else torch.float32
         self.cfg = MFCCConfig(width=width, nfft=nfft, samplerate=samplerate, nfilters=nfilters,
-                              nceptrums=nceptrums, mode=MODE_INT)
+                              nceptrums=nceptrums, mode=MODE_INT if mode == "int" else MODE_FP32,
+                              mel_floor=float(mel_floor) if mode == "fp32" else 0.0)
         self.width, self.nfft, self.samplerate = width, nfft, samplerate
         self.nfilters, self.nceptrums = nfilters, nceptrums
         if not torch.cuda.is_available():
@@ -51,16 +57,22 @@ class MFCC:
                                    "cuda:%d" % torch.cuda.current_device())
         with torch.cuda.device(self.device):
             self._h = Handle(self.cfg)
-        from . import stages as S   # stage operators share this handle
-        self.preemph = S.Preemph(width, _handle=self._h, device=self.device)
-        self.frame = S.Frame(width, nfft, nfft // 3, nfft, _handle=self._h, device=self.device)
-        self.window = S.WindowHamming(width, nfft, 8, _handle=self._h, device=self.device)
-        self.fft_stream = S.FftStream(width, nfft, _handle=self._h, device=self.device)
-        self.powspec = S.PowerSpectrum(width, 30, _handle=self._h, device=self.device)
+        from . import stages as S   # stage operators share the integer-mode handle
+        if mode == "int":
+            hs = self._h
+        else:
+            with torch.cuda.device(self.device):
+                hs = Handle(MFCCConfig(width=width, nfft=nfft, samplerate=samplerate,
+                                       nfilters=nfilters, nceptrums=nceptrums))
+        self.preemph = S.Preemph(width, _handle=hs, device=self.device)
+        self.frame = S.Frame(width, nfft, nfft // 3, nfft, _handle=hs, device=self.device)
+        self.window = S.WindowHamming(width, nfft, 8, _handle=hs, device=self.device)
+        self.fft_stream = S.FftStream(width, nfft, _handle=hs, device=self.device)
+        self.powspec = S.PowerSpectrum(width, 30, _handle=hs, device=self.device)
         self.filterbank = S.FilterBank(30, 16, None, 18, samplerate, nfft, nfilters,
-                                       _handle=self._h, device=self.device)
-        self.log2 = S.Log2Fix(16, 15, _handle=self._h, device=self.device)
-        self.dct_stream = S.DCTStream(width, nfilters, _handle=self._h, device=self.device)
+                                       _handle=hs, device=self.device)
+        self.log2 = S.Log2Fix(16, 15, _handle=hs, device=self.device)
+        self.dct_stream = S.DCTStream(width, nfilters, _handle=hs, device=self.device)
         self.discard = S.Discard(width, 0, nceptrums)
         self._state = None
 
@@ -86,12 +98,14 @@ class MFCC:
             raise ValueError("n_frames must be >= 0")
         nc = self.nceptrums
         if out is None:
-            out = torch.empty((B, K, nc), dtype=torch.int16, device=self.device)
-        elif out.shape != (B, K, nc) or out.dtype != torch.int16 or not out.is_contiguous():
-            raise ValueError("out must be a contiguous int16 [B, K, nceptrums] tensor")
+            out = torch.empty((B, K, nc), dtype=self.out_dtype, device=self.device)
+        elif out.shape != (B, K, nc) or out.dtype != self.out_dtype or not out.is_contiguous():
+            raise ValueError("out must be a contiguous %s [B, K, nceptrums] tensor" % self.out_dtype)
         tp = None
         tensors = None
         if taps:
+            if self.mode != "int":
+                raise ValueError("taps are an integer-mode feature")
             if B != 1:
                 raise ValueError("taps need a single clip")
             nf, nb = self.nfilters, self.nfft // 2
@@ -126,7 +140,10 @@ class MFCC:
         K = self.num_frames(N) if n_frames is None else int(n_frames)
         nc = self.nceptrums
         if out is None:
-            out = torch.empty((B, K, nc), dtype=torch.int16)
+            out = torch.empty((B, K, nc), dtype=self.out_dtype)
+        elif out.shape != (B, K, nc) or out.dtype != self.out_dtype or not out.is_contiguous() \
+                or out.device.type != "cpu":
+            raise ValueError("out must be a contiguous CPU %s [B, K, nceptrums] tensor" % self.out_dtype)
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().mfcc_b200_run_host(
                 self._h.ptr, C.c_void_p(x.data_ptr()), N, N, B, K, C.c_void_p(out.data_ptr()),
@@ -158,7 +175,7 @@ class MFCC:
             self.reset(S)
         hop = hop.contiguous()
         if out is None:
-            out = torch.empty((S, self.nceptrums), dtype=torch.int16, device=self.device)
+            out = torch.empty((S, self.nceptrums), dtype=self.out_dtype, device=self.device)
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().mfcc_b200_step(
                 self._h.ptr, C.c_void_p(self._state.data_ptr()), C.c_void_p(hop.data_ptr()), S,

@@ -175,3 +175,34 @@ def mel_segment_bounds(nfilters: int = 32, nfft: int = 512, samplerate: float = 
         out[g, 1] = idx[-1]
         assert close[idx[-1]] == 1 and not close[idx[:-1]].any()
     return out
+
+
+# ----------------------------------------------------------------------------- fp32 mode
+# Tables of the float pipeline of notebook/MFCC-INT.ipynb (cells 4, 7, 10), built in
+# float64 and handed to the library as float32.
+
+def f_window(nfft: int = 512) -> np.ndarray:
+    """Periodic Hamming, ``get_window("hamm", nfft, fftbins=True)`` (cell 4):
+    0.54 - 0.46 cos(2 pi n / nfft)."""
+    n = np.arange(nfft)
+    return 0.54 - 0.46 * np.cos(2.0 * np.pi * n / nfft)
+
+
+def f_mel_filters(nfilters: int = 32, nfft: int = 512, samplerate: float = 16e3) -> np.ndarray:
+    """Dense [nfilters][nfft/2+1] triangles of ``get_filters`` (cell 7): linspace(0, 1)
+    up to the centre point, linspace(1, 0) down, on the same points as the RTL."""
+    p = mel_points(nfilters, nfft, samplerate)
+    f = np.zeros((nfilters, nfft // 2 + 1))
+    for n in range(nfilters):
+        f[n, p[n]:p[n + 1]] = np.linspace(0, 1, p[n + 1] - p[n])
+        f[n, p[n + 1]:p[n + 2]] = np.linspace(1, 0, p[n + 2] - p[n + 1])
+    return f
+
+
+def f_dct_matrix(n: int = 32) -> np.ndarray:
+    """Orthonormal DCT-II matrix D[k][m] (``scipy.fft.dct(type=2, norm="ortho")``, cell 10)."""
+    k = np.arange(n)[:, None]
+    m = np.arange(n)[None, :]
+    d = np.cos(np.pi * (m + 0.5) * k / n) * np.sqrt(2.0 / n)
+    d[0] *= np.sqrt(0.5)
+    return d

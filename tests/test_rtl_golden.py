@@ -177,8 +177,11 @@ def test_cuda_stage_operators_match_rtl_stage_vectors(sv):
     d = M.DCTStream(16, 32, device=dev)
     got = d(T(sv["dct32_in"].astype(np.uint16).view(np.int16), np.int16)).cpu().numpy()
     assert np.array_equal(got, s16(sv["dct32_out"]))
+    got = d(T(sv["dct32s_in"], np.int16)).cpu().numpy()                  # full signed range
+    assert np.array_equal(got, s16(sv["dct32s_out"]))
     got = M.DCTStream(16, 16, device=dev)(T(sv["dct16_in"].astype(np.uint16).view(np.int16), np.int16))
     assert np.array_equal(got.cpu().numpy(), s16(sv["dct16_out"]))
-    p = sv["power_in"]
-    got = M.PowerSpectrum(16, 30, device=dev)(T(p[None], np.int16)).cpu().numpy().view(np.uint32)
-    assert np.array_equal(got[0], sv["power_out"])
+    p = np.zeros((1, 256, 2), dtype=np.int64)                   # the operator takes whole frames
+    p[0, :len(sv["power_in"])] = sv["power_in"]
+    got = M.PowerSpectrum(16, 30, device=dev)(T(p, np.int16)).cpu().numpy().view(np.uint32)
+    assert np.array_equal(got[0, :len(sv["power_out"])], sv["power_out"])
