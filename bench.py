@@ -172,6 +172,53 @@ def run_reference(args, rank, world):
         "gpu_launches": 0}))
 
 
+def stream_latency(op, dev, n_streams=4096, steps=10000, warmup=200):
+    """BASELINE.json configs[4]: `n_streams` live streams, one
+    170-sample hop per stream per step, the step captured once in a CUDA graph (H2D of the
+    hops from pinned memory, the streaming kernel, D2H of the cepstrum columns).  Returns
+    p50/p99 of the device time per step (CUDA events around the replay) and of the host
+    wall time per step (perf_counter around replay + stream synchronize)."""
+    import torch
+    hop_h = torch.randint(-3000, 3000, (n_streams, 170), dtype=torch.int16).pin_memory()
+    out_h = torch.empty((n_streams, op.nceptrums), dtype=op.out_dtype).pin_memory()
+    hop_d = torch.empty((n_streams, 170), dtype=torch.int16, device=dev)
+    out_d = torch.empty((n_streams, op.nceptrums), dtype=op.out_dtype, device=dev)
+    op.reset(n_streams)
+    st = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            hop_d.copy_(hop_h, non_blocking=True)
+            op.step(hop_d, out=out_d)
+            out_h.copy_(out_d, non_blocking=True)
+        st.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            hop_d.copy_(hop_h, non_blocking=True)
+            op.step(hop_d, out=out_d)
+            out_h.copy_(out_d, non_blocking=True)
+        for _ in range(warmup):
+            g.replay()
+        st.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+        wall = []
+        ev[0].record(st)
+        for i in range(steps):
+            t0 = time.perf_counter()
+            g.replay()
+            ev[i + 1].record(st)
+            st.synchronize()
+            wall.append(time.perf_counter() - t0)
+    dev_us = sorted(ev[i].elapsed_time(ev[i + 1]) * 1e3 for i in range(steps))
+    wall_us = sorted(w * 1e6 for w in wall)
+    pick = lambda a, q: a[min(len(a) - 1, int(q * len(a)))]
+    return {"workload": "C5: %d live streams, one 170-sample hop per stream per step, CUDA graph "
+                        "(H2D hops + step kernel + D2H columns)" % n_streams,
+            "steps": steps, "device_us_p50": pick(dev_us, 0.5), "device_us_p99": pick(dev_us, 0.99),
+            "host_us_p50": pick(wall_us, 0.5), "host_us_p99": pick(wall_us, 0.99),
+            "realtime_budget_us": 170 / 16000 * 1e6,
+            "frames_per_sec_at_p50": n_streams / (pick(wall_us, 0.5) * 1e-6)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -181,6 +228,9 @@ def main():
     ap.add_argument("--clips", type=int, default=N_CLIPS, help="clips per GPU (default: configs[1])")
     ap.add_argument("--e2e-clips", type=int, default=2048)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the fp32-mode and streaming-latency figures (rank 0, N=1 only)")
+    ap.add_argument("--stream-steps", type=int, default=10000)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -253,6 +303,31 @@ def main():
     e2e_value = ne * K * world * e_steps / float(te.item())
     e2e_ok = bool(torch.equal(oh.to(dev), out[:ne]))
 
+    extras = {}
+    if world == 1 and not args.no_extras:
+        # fp32 mode on the same clips (config C3's throughput leg; parity is in tests/)
+        del xh, oh
+        opf = mfcc_b200.MFCC(nfilters=NFILT, nceptrums=NCEP, mode="fp32", mel_floor=1e-3, device=dev)
+        outf = torch.empty((args.clips, K, NCEP), dtype=torch.float32, device=dev)
+        for _ in range(3):
+            opf(x, out=outf)
+        torch.cuda.synchronize()
+        fsteps = max(3, min(args.steps, 5))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(fsteps):
+            opf(x, out=outf)
+        e1.record()
+        torch.cuda.synchronize()
+        tf = e0.elapsed_time(e1) * 1e-3 / fsteps
+        extras["fp32"] = {"value": frames_rank / tf, "unit": "frames/s", "ms_per_step": tf * 1e3,
+                          "steps": fsteps, "bytes_per_frame": 170 * 2 + NCEP * 4,
+                          "achieved_gbs": frames_rank * (170 * 2 + NCEP * 4) / tf / 1e9,
+                          "kernel": "mfcc_f32_fused<32>", "finite": bool(torch.isfinite(outf[:64]).all())}
+        del outf
+        extras["streaming"] = stream_latency(op, dev, 4096, args.stream_steps)
+        extras["streaming_fp32"] = stream_latency(opf, dev, 4096, max(1000, args.stream_steps // 5))
+
     if rank == 0:
         peaks = {}
         try:
@@ -283,6 +358,9 @@ def main():
                     "h2d_bytes_per_step": ne * N_SAMPLES * 2, "d2h_bytes_per_step": ne * K * NCEP * 2},
             "gpu_launches": int(launches), "clocks": clocks,
         }
+        if extras:
+            extras["fp32"]["hbm_frac"] = extras["fp32"]["achieved_gbs"] / peak
+            line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             from oracle import ref_c as RC
             thr = RC.max_threads()

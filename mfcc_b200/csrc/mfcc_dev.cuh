@@ -24,10 +24,12 @@ constexpr unsigned FULL = 0xffffffffu;
 struct alignas(16) DevTables {
     int2     twB[128];       // stages 4..7, doubled (2re, 2im): [16 | 16 | 32 | 64] entries
     int2     tw8[256];       // stage 8, doubled, natural order
-    uint32_t melw[256];      // weight per bin, filterbank.py:90-115
+    uint2    melab[672];     // FilterBank weights, padded per segment: see mel_warp()
+    uint32_t seg0_wa[4];     // segment 0 (feeds filter 0 only)
+    uint16_t logfrac[2048];  // Log2Fix fraction bits 10..1 for every 12-bit mantissa: see log2fix_tab()
     int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
     int2     dct_twf[32];    // final DCT stage, lane j = bin j, doubled
-    int16_t  curve[512];     // window multipliers, window.py:59-115
+    uint16_t curve[512];     // window multipliers (9 bits, unsigned), window.py:59-115
     int16_t  seg_first[40];  // first bin of mel segment g
     int16_t  seg_close[40];  // closing bin of mel segment g
     int32_t  mel_lo_bit;     // filterbank.py:122
@@ -60,36 +62,67 @@ __host__ __device__ constexpr int brev4(int v) {
 // w2r, w2i are the doubled twiddle components.
 struct Bf { unsigned s0r, s0i, s1r, s1i; };
 
-__device__ __forceinline__ Bf bf_core(int x0r, int x0i, int x1r, int x1i, int w2r, int w2i) {
-    unsigned qr = (unsigned)(x1r * w2r) - (unsigned)(x1i * w2i) + 16382u;
-    unsigned qi = (unsigned)(x1i * w2r) + (unsigned)(x1r * w2i) + 16382u;
-    unsigned br = (unsigned)x0r << 15;
-    unsigned bi = (unsigned)x0i << 15;
+// nw2i = -w2i is passed in so that the subtraction of the imaginary product is a
+// multiply-add too (twiddles are table entries or compile-time constants: free).
+__device__ __forceinline__ Bf bf_core(int x0r, int x0i, int x1r, int x1i, int w2r, int w2i, int nw2i) {
+    unsigned qr = (unsigned)(x1r * w2r) + 16382u;
+    qr += (unsigned)(x1i * nw2i);
+    unsigned qi = (unsigned)(x1i * w2r) + 16382u;
+    qi += (unsigned)(x1r * w2i);
     Bf o;
-    o.s0r = br + qr;
-    o.s0i = bi + qi;
-    o.s1r = br - qr + 32766u;
-    o.s1i = bi - qi + 32766u;
+    o.s0r = (unsigned)(x0r * 32768) + qr;
+    o.s0i = (unsigned)(x0i * 32768) + qi;
+    o.s1r = (unsigned)(x0r * 32768) + (32766u - qr);
+    o.s1i = (unsigned)(x0i * 32768) + (32766u - qi);
     return o;
 }
 
 // in-place, unpacked (sign-extended 16-bit values in 32-bit registers)
-__device__ __forceinline__ void bf(int &x0r, int &x0i, int &x1r, int &x1i, int w2r, int w2i) {
-    Bf o = bf_core(x0r, x0i, x1r, x1i, w2r, w2i);
+__device__ __forceinline__ void bf(int &x0r, int &x0i, int &x1r, int &x1i, int w2r, int w2i, int nw2i) {
+    Bf o = bf_core(x0r, x0i, x1r, x1i, w2r, w2i, nw2i);
     x0r = (int)o.s0r >> 16; x0i = (int)o.s0i >> 16;
     x1r = (int)o.s1r >> 16; x1i = (int)o.s1i >> 16;
 }
+__device__ __forceinline__ void bf(int &x0r, int &x0i, int &x1r, int &x1i, int w2r, int w2i) {
+    bf(x0r, x0i, x1r, x1i, w2r, w2i, -w2i);
+}
 
 // packed outputs (re in the low half, im in the high half): one PRMT per value
-__device__ __forceinline__ void bf_pk(int x0r, int x0i, int x1r, int x1i, int w2r, int w2i,
+__device__ __forceinline__ void bf_pk(int x0r, int x0i, int x1r, int x1i, int w2r, int w2i, int nw2i,
                                       unsigned &p0, unsigned &p1) {
-    Bf o = bf_core(x0r, x0i, x1r, x1i, w2r, w2i);
+    Bf o = bf_core(x0r, x0i, x1r, x1i, w2r, w2i, nw2i);
     p0 = __byte_perm(o.s0r, o.s0i, 0x7632);
     p1 = __byte_perm(o.s1r, o.s1i, 0x7632);
+}
+__device__ __forceinline__ void bf_pk(int x0r, int x0i, int x1r, int x1i, int w2r, int w2i,
+                                      unsigned &p0, unsigned &p1) {
+    bf_pk(x0r, x0i, x1r, x1i, w2r, w2i, -w2i, p0, p1);
+}
+
+// Trivial twiddles.  For tw = (16384, 0) the RTL's t = (x1 * 16384 + 8191) >> 14 is x1
+// itself, for tw = (0, -16384) it is (x1.im, -x1.re) (fft.py:93-96, :152-180; SURVEY.md
+// a5), so the butterfly is y = (x0 +- t) >> 1.  The sum of two 16-bit values halved
+// fits 16 bits: the 16-bit wrap of :188-191 cannot trigger.  Real operands (the frame
+// is real, fft_stream.py:33) stay real through W^0 butterflies.
+__device__ __forceinline__ void bf1_rr(int &x0, int &x1) {                 // W^0, real (+) real
+    const int s = x0 + x1, d = x0 - x1;
+    x0 = s >> 1; x1 = d >> 1;
+}
+__device__ __forceinline__ void bfj_rr(int &x0r, int &x0i, int &x1r, int &x1i) {   // -j, real (+) real
+    const int a = x0r >> 1, b = x1r;                                       // t = (0, -x1)
+    x0r = a; x0i = (-b) >> 1;
+    x1r = a; x1i = b >> 1;
+}
+__device__ __forceinline__ void bfj_cc(int &x0r, int &x0i, int &x1r, int &x1i) {   // -j, complex
+    const int tr = x1i, ti = -x1r;
+    const int a = x0r, b = x0i;
+    x0r = (a + tr) >> 1; x0i = (b + ti) >> 1;
+    x1r = (a - tr) >> 1; x1i = (b - ti) >> 1;
 }
 
 __device__ __forceinline__ int lo16(unsigned w) { return (int)(short)(w & 0xffffu); }
 __device__ __forceinline__ int hi16(unsigned w) { return (int)w >> 16; }
+__device__ __forceinline__ unsigned pk16(int re, int im) { return __byte_perm((unsigned)re, (unsigned)im, 0x5410); }
 
 // exchange 1: pass-A lane `row` owns positions 16*row + col.  The skew makes both
 // the 128-bit row stores and the column reads of pass B conflict free.
@@ -104,26 +137,36 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
                                             int lane, int (&re)[8], int (&im)[8])
 {
     int xi[16];
+    // ---- stage 0: W^0 everywhere, real operands
 #pragma unroll
-    for (int l = 0; l < 16; ++l) xi[l] = 0;                  // fft_stream.py:33
-
-    // ---- stages 0..2 in registers; twiddle index k*(256>>s) = 32*(k*(8>>s))
+    for (int l = 0; l < 16; l += 2) bf1_rr(xr[l], xr[l + 1]);
+    // ---- stage 1: W^0 (real stays real) and -j (real pair -> complex pair)
 #pragma unroll
-    for (int s = 0; s < 3; ++s) {
-        const int half = 1 << s;
-#pragma unroll
-        for (int l = 0; l < 16; ++l) {
-            if (l & half) continue;
-            const int t = (l & (half - 1)) * (8 >> s);
-            bf(xr[l], xi[l], xr[l + half], xi[l + half], 2 * TWA_RE[t], 2 * TWA_IM[t]);
-        }
+    for (int l = 0; l < 16; l += 4) {
+        bf1_rr(xr[l], xr[l + 2]);
+        bfj_rr(xr[l + 1], xi[l + 1], xr[l + 3], xi[l + 3]);
     }
-    // ---- stage 3, packed straight into the exchange buffer
+    // ---- stage 2: k = 0 W^0 (real), 1 W^64, 2 -j (real -> complex), 3 W^192
+#pragma unroll
+    for (int l = 0; l < 16; l += 8) {
+        bf1_rr(xr[l], xr[l + 4]);
+        bf(xr[l + 1], xi[l + 1], xr[l + 5], xi[l + 5], 2 * TWA_RE[2], 2 * TWA_IM[2], -2 * TWA_IM[2]);
+        bfj_rr(xr[l + 2], xi[l + 2], xr[l + 6], xi[l + 6]);
+        bf(xr[l + 3], xi[l + 3], xr[l + 7], xi[l + 7], 2 * TWA_RE[6], 2 * TWA_IM[6], -2 * TWA_IM[6]);
+    }
+    // ---- stage 3, packed straight into the exchange buffer: slots 0 and 8 are still
+    //      real, 4 and 12 turn complex through -j, the other six are general
     {
         unsigned pk[16];
+        bf1_rr(xr[0], xr[8]);
+        pk[0] = (unsigned)xr[0] & 0xffffu; pk[8] = (unsigned)xr[8] & 0xffffu;
+        bfj_rr(xr[4], xi[4], xr[12], xi[12]);
+        pk[4] = pk16(xr[4], xi[4]); pk[12] = pk16(xr[12], xi[12]);
 #pragma unroll
-        for (int l = 0; l < 8; ++l)
-            bf_pk(xr[l], xi[l], xr[l + 8], xi[l + 8], 2 * TWA_RE[l], 2 * TWA_IM[l], pk[l], pk[l + 8]);
+        for (int l = 1; l < 8; ++l) {
+            if (l == 4) continue;
+            bf_pk(xr[l], xi[l], xr[l + 8], xi[l + 8], 2 * TWA_RE[l], 2 * TWA_IM[l], -2 * TWA_IM[l], pk[l], pk[l + 8]);
+        }
         uint4 *row = reinterpret_cast<uint4 *>(xbuf + xa_addr(lane, 0));
 #pragma unroll
         for (int q = 0; q < 4; ++q) row[q] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
@@ -141,25 +184,28 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
     // Indices >= 128 are the stored entry turned by -j: (re, im) -> (im, -re)  (fft.py:55-59)
     {   // stage 4: one twiddle per lane
         const int2 w = tab->twB[l4];
+        const int nwy = -w.y;
 #pragma unroll
-        for (int m = 0; m < 16; m += 2) bf(xr[m], xi[m], xr[m + 1], xi[m + 1], w.x, w.y);
+        for (int m = 0; m < 16; m += 2) bf(xr[m], xi[m], xr[m + 1], xi[m + 1], w.x, w.y, nwy);
     }
     {   // stage 5
         const int2 w = tab->twB[16 + l4];
+        const int nwy = -w.y, nwx = -w.x;
 #pragma unroll
         for (int m = 0; m < 16; m += 4) {
-            bf(xr[m], xi[m], xr[m + 2], xi[m + 2], w.x, w.y);
-            bf(xr[m + 1], xi[m + 1], xr[m + 3], xi[m + 3], w.y, -w.x);
+            bf(xr[m], xi[m], xr[m + 2], xi[m + 2], w.x, w.y, nwy);
+            bf(xr[m + 1], xi[m + 1], xr[m + 3], xi[m + 3], w.y, nwx, w.x);    // W * (-j)
         }
     }
     {   // stage 6
 #pragma unroll
         for (int mm = 0; mm < 2; ++mm) {
             const int2 w = tab->twB[32 + mm * 16 + l4];
+            const int nwy = -w.y, nwx = -w.x;
 #pragma unroll
             for (int m = 0; m < 16; m += 8) {
-                bf(xr[m + mm], xi[m + mm], xr[m + mm + 4], xi[m + mm + 4], w.x, w.y);
-                bf(xr[m + mm + 2], xi[m + mm + 2], xr[m + mm + 6], xi[m + mm + 6], w.y, -w.x);
+                bf(xr[m + mm], xi[m + mm], xr[m + mm + 4], xi[m + mm + 4], w.x, w.y, nwy);
+                bf(xr[m + mm + 2], xi[m + mm + 2], xr[m + mm + 6], xi[m + mm + 6], w.y, nwx, w.x);
             }
         }
     }
@@ -169,8 +215,8 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
         for (int mm = 0; mm < 4; ++mm) {
             const int2 w = tab->twB[64 + mm * 16 + l4];
             unsigned a0, a1, b0, b1;
-            bf_pk(xr[mm], xi[mm], xr[mm + 8], xi[mm + 8], w.x, w.y, a0, a1);
-            bf_pk(xr[mm + 4], xi[mm + 4], xr[mm + 12], xi[mm + 12], w.y, -w.x, b0, b1);
+            bf_pk(xr[mm], xi[mm], xr[mm + 8], xi[mm + 8], w.x, w.y, -w.y, a0, a1);
+            bf_pk(xr[mm + 4], xi[mm + 4], xr[mm + 12], xi[mm + 12], w.y, -w.x, w.x, b0, b1);
             dst[16 * mm] = a0;        dst[16 * (mm + 8)] = a1;
             dst[16 * (mm + 4)] = b0;  dst[16 * (mm + 12)] = b1;
         }
@@ -192,42 +238,83 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
 }
 
 // ---------------------------------------------------------------------------------
-// FilterBank.  pw[0..255] in shared memory.  Returns the 16-bit mel value of filter
-// (lane mod NF).  Segment g = bins seg_first[g] .. seg_close[g]; with
-//   A_g = sum d*w over the non-closing bins, D_g = sum d, PK_g = d at the closing bin
-// the register the hardware reads at the close of segment g is
-//   A_{g-1} + (PK_{g-1} << 30) + (D_g << 30) - A_g         filterbank.py:119-142
+// FilterBank.  pw[0..255] in shared memory (the buffer behind it is readable up to
+// pw[255 + MAXSEG]).  Returns the 16-bit mel value of filter (lane mod NF).
+// Segment g = bins seg_first[g] .. seg_close[g].  With A_g = sum d*w over its non-closing
+// bins, D_g = sum d over them and PK_g = d at the closing bin, the register the hardware
+// reads at the close of segment g is (filterbank.py:119-142)
+//     A_{g-1} + (PK_{g-1} << 30)  +  (D_g << 30) - A_g
 // of which bits lo_bit .. lo_bit+15 are kept (:122): arithmetic modulo 2^64 is exact.
+// Both halves are plain weighted sums over one segment:
+//     Abar_g = sum d * wa,  wa = w on non-closing bins, 2^30 on the closing bin
+//     Bbar_g = sum d * wb,  wb = 2^30 - w on non-closing bins, 0 on the closing bin
+// so lane g-1 walks segment g once with two 64-bit multiply-adds per bin and takes
+// Abar_{g-1} from its neighbour.  melab[j * NF + lane] = (wa, wb) of the j-th bin of the
+// lane's segment, zero past its end: every lane runs the same MAXSEG steps, no branches.
 template <int NF>
 __device__ __forceinline__ unsigned mel_warp(const unsigned *pw, const DevTables *tab, int lane)
 {
-    // segment 0 (output suppressed, filterbank.py:139) is cheap; every lane does it
-    unsigned long long a0 = 0;
-    const int c0 = tab->seg_close[0];
-    for (int b = tab->seg_first[0]; b < c0; ++b) a0 += (unsigned long long)pw[b] * tab->melw[b];
-    const unsigned pk0 = pw[c0];
-
-    const int g = (lane & (NF - 1)) + 1;
-    const int first = tab->seg_first[g], cl = tab->seg_close[g];
-    unsigned long long a = 0;
-    unsigned d = 0;
-    for (int b = first; b < cl; ++b) {
-        const unsigned v = pw[b];
-        a += (unsigned long long)v * tab->melw[b];
-        d += v;
+    constexpr int MAXSEG = (NF == 32) ? 21 : 42;
+    const int li = lane & (NF - 1);
+    const unsigned *p = pw + tab->seg_first[li + 1];
+    unsigned long long a = 0, b = 0;
+    if (NF == 32) {
+#pragma unroll
+        for (int j = 0; j < MAXSEG; ++j) {
+            const unsigned d = p[j];
+            const uint2 w = tab->melab[j * NF + li];
+            a += (unsigned long long)d * w.x;
+            b += (unsigned long long)d * w.y;
+        }
+    } else {
+        // 16 filters: the two half-warps split the steps of each segment
+        const int j0 = (lane >> 4) * (MAXSEG / 2);
+#pragma unroll
+        for (int j = 0; j < MAXSEG / 2; ++j) {
+            const unsigned d = p[j0 + j];
+            const uint2 w = tab->melab[(j0 + j) * NF + li];
+            a += (unsigned long long)d * w.x;
+            b += (unsigned long long)d * w.y;
+        }
+        a += __shfl_xor_sync(FULL, a, 16);
+        b += __shfl_xor_sync(FULL, b, 16);
     }
-    const unsigned pk = pw[cl];
+    // segment 0 (its own output is suppressed, filterbank.py:139) feeds filter 0
+    unsigned long long a0 = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) a0 += (unsigned long long)pw[j] * tab->seg0_wa[j];
     unsigned long long pa = __shfl_up_sync(FULL, a, 1);
-    unsigned ppk = __shfl_up_sync(FULL, pk, 1);
-    if ((lane & (NF - 1)) == 0) { pa = a0; ppk = pk0; }
-    const unsigned e = ppk + d;
-    const unsigned long long x = pa - a + ((unsigned long long)e << 30);
+    if (li == 0) pa = a0;
+    const unsigned long long x = pa + b;
     return (unsigned)(x >> tab->mel_lo_bit) & 0xffffu;
 }
 
 // Log2Fix(16, 15) -> Log2FixCalc(27, 11), log.py:123-126, :57-62, :80-102, :133.
 // The SHIFT-RIGHT loop runs floor(log2 m) times; the ten squarings set fraction
 // bits 10..1 (bit 0 is never reached: cnt stops at 1).
+__host__ __device__ __forceinline__ unsigned log2fix_frac(unsigned z)
+{
+    unsigned frac = 0;
+    for (int it = 0; it < 10; ++it) {
+        const unsigned c = z * z;
+        const unsigned bit = (c >> 23) & 1u;
+        z = c >> (11 + bit);
+        frac = (frac << 1) | bit;
+    }
+    return frac;
+}
+
+// Same function through the table: the ten squarings depend only on the normalised
+// 12-bit mantissa z in [2048, 4096), so their result is tabulated (logfrac[z - 2048],
+// filled by mfcc_b200_create() with log2fix_frac).
+__device__ __forceinline__ unsigned log2fix_tab(unsigned m, const uint16_t *logfrac)
+{
+    const unsigned mm = m ? m : 1u;
+    const int sh = 31 - __clz(mm);
+    const unsigned z = (mm << 11) >> sh;
+    return (((unsigned)sh << 11) + ((unsigned)logfrac[z - 2048] << 1)) & 0x7fffu;
+}
+
 __device__ __forceinline__ unsigned log2fix_lane(unsigned m)
 {
     const unsigned mm = m ? m : 1u;

@@ -17,21 +17,22 @@ namespace mfccf {
 constexpr int NFFT = 512;
 constexpr int HOP = 170;
 constexpr int NBINS1 = 257;            // the notebook keeps bins 0..256 (cell 5)
-constexpr int MELW_MAX = 608;          // sum of the filter spans (2 * 257 plus slack)
-constexpr int XWF = 848;               // 32-bit words of the per-warp exchange buffer
+constexpr int XWF = 1040;              // 32-bit words of the per-warp exchange buffer
 constexpr int T1_STRIDE = 36;          // float2 per row of the first transpose
 constexpr int PW_OFF = 576;            // power spectrum lives behind the transpose area
+constexpr int PW_WORDS = XWF - PW_OFF; // padded power-spectrum area: see DevTablesF::paddr
 constexpr unsigned FULL = 0xffffffffu;
 
 struct alignas(16) DevTablesF {
-    float  window[NFFT];               // hamming(512, periodic) / 32: see load_z()
-    float2 tw256[256];                 // exp(-2 pi i k / 256)
+    float  window[NFFT];               // hamming(512, periodic) / 32: see emph_win()
+    float2 twA[8 * 32];                // [k1][lane]  exp(-2 pi i lane k1 / 256)
+    float2 twB[8 * 4];                 // [p][c]      exp(-2 pi i c p / 32)
     float2 tw512[132];                 // exp(-2 pi i k / 512), k = 0..128
-    float  dct[32 * 32];               // dct[n * 32 + k] = D[k][n] (orthonormal DCT-II)
-    float  melw[MELW_MAX];             // the non-zero span of every filter, concatenated
-    int16_t mel_lo[32];                // first bin of filter m's span
-    int16_t mel_n[32];                 // bins in the span
-    int16_t mel_off[32];               // offset of the span in melw[]
+    float  dct[16 * 32];               // dct[n * 32 + k] = D[k][n], n < nfilters / 2 (the rest by symmetry)
+    float2 melw[672];                  // [step][lane] (rise weight, fall weight) of the lane's segment
+    float  seg0w[4];                   // rise weights of segment 0 (filter 0)
+    uint16_t paddr[264];               // word address of bin b in the padded power area
+    uint16_t seg_base[32];             // address of the first bin of lane's segment (segment lane+1)
     float  mel_floor;                  // energies are clamped to this before log2 (0 = off)
     int32_t pad[3];
 };
@@ -112,7 +113,7 @@ __device__ __forceinline__ void power_warp_f32(const int16_t *raw, float *xb, co
     for (int j = 0; j < 8; ++j) {
         const int k1 = brev3(j);
         float2 y = v[j];
-        if (k1) y = cmul(y, tab->tw256[lane * k1]);
+        if (k1) y = cmul(y, tab->twA[k1 * 32 + lane]);
         xc[k1 * T1_STRIDE + lane] = y;
     }
     __syncwarp();
@@ -131,7 +132,7 @@ __device__ __forceinline__ void power_warp_f32(const int16_t *raw, float *xb, co
     for (int j = 0; j < 8; ++j) {
         const int p = brev3(j);
         float2 y = v[j];
-        if (p) y = cmul(y, tab->tw256[8 * c * p]);
+        if (p) y = cmul(y, tab->twB[p * 4 + c]);
         float2 o;
         o.x = __shfl_xor_sync(FULL, y.x, 2);
         o.y = __shfl_xor_sync(FULL, y.y, 2);
@@ -156,30 +157,72 @@ __device__ __forceinline__ void power_warp_f32(const int16_t *raw, float *xb, co
         const float2 G = make_float2(0.5f * (A.y + B.y), -0.5f * (A.x - B.x));
         const float2 T = cmul(G, w);
         const float2 X0 = cadd(F, T), X1 = csub(F, T);
-        pw[k] = (X0.x * X0.x + X0.y * X0.y) * SC;
-        pw[256 - k] = (X1.x * X1.x + X1.y * X1.y) * SC;      // k = 0 gives bin 256
+        pw[tab->paddr[k]] = (X0.x * X0.x + X0.y * X0.y) * SC;
+        pw[tab->paddr[256 - k]] = (X1.x * X1.x + X1.y * X1.y) * SC;      // k = 0 gives bin 256
     }
     if (lane == 0) {                                         // bin 128: W512^128 = -j
         const float2 A = xc[zaddr(128)];
-        pw[128] = (A.x * A.x + A.y * A.y) * SC;
+        pw[tab->paddr[128]] = (A.x * A.x + A.y * A.y) * SC;
     }
     __syncwarp();
 }
 
-// mel -> log2 -> DCT-II of the power spectrum in pw[]; lane k returns coefficient k.
+// mel -> log2 -> DCT-II of the power spectrum in pw[] (padded layout); lane k returns
+// coefficient k.  The filters are triangles (cell 7): bin b of segment g (the bins
+// between two filter points) carries the rising weight of filter g and the falling
+// weight of filter g-1, so lane g-1 walks segment g once with two multiply-adds per
+// bin (weights zero-padded to MAXSEG steps: no branches) and filter m is the rising sum
+// of segment m, taken from the neighbouring lane, plus the falling sum of segment m+1.
+// The padded layout (DevTablesF::paddr) starts every segment in a bank of its own, so the
+// 32 lanes read 32 different banks at every step.
 template <int NF>
-__device__ __forceinline__ float cepstrum_warp_f32(const float *pw, const DevTablesF *tab, int lane)
+__device__ __forceinline__ float cepstrum_warp_f32(float *pw, float *lbuf, const DevTablesF *tab, int lane)
 {
-    const int m = lane & (NF - 1);
-    const int lo = tab->mel_lo[m], n = tab->mel_n[m];
-    const float *w = tab->melw + tab->mel_off[m];
-    float acc = 0.0f;
-    for (int j = 0; j < n; ++j) acc = fmaf(w[j], pw[lo + j], acc);
-    const float L = __log2f(fmaxf(acc, tab->mel_floor));
+    constexpr int MAXSEG = (NF == 32) ? 21 : 42;
+    const int li = lane & (NF - 1);
+    const float *p = pw + tab->seg_base[li];
+    float u = 0.0f, v = 0.0f;
+    if (NF == 32) {
+#pragma unroll
+        for (int j = 0; j < MAXSEG; ++j) {
+            const float d = p[j];
+            const float2 w = tab->melw[j * NF + li];
+            u = fmaf(d, w.x, u);
+            v = fmaf(d, w.y, v);
+        }
+    } else {
+        const int j0 = (lane >> 4) * (MAXSEG / 2);
+#pragma unroll
+        for (int j = 0; j < MAXSEG / 2; ++j) {
+            const float d = p[j0 + j];
+            const float2 w = tab->melw[(j0 + j) * NF + li];
+            u = fmaf(d, w.x, u);
+            v = fmaf(d, w.y, v);
+        }
+        u += __shfl_xor_sync(FULL, u, 16);
+        v += __shfl_xor_sync(FULL, v, 16);
+    }
+    float u0 = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) u0 = fmaf(pw[tab->paddr[j]], tab->seg0w[j], u0);
+    float up = __shfl_up_sync(FULL, u, 1);
+    if (li == 0) up = u0;
+    const float L = __log2f(fmaxf(up + v, tab->mel_floor));
+    // orthonormal DCT-II with D[k][NF-1-n] = (-1)^k D[k][n]: NF/2 multiply-adds per lane
+    lbuf[lane] = L;
+    __syncwarp();
+    const float sg = (li & 1) ? -1.0f : 1.0f;
     float out = 0.0f;
 #pragma unroll
-    for (int nn = 0; nn < NF; ++nn)
-        out = fmaf(__shfl_sync(FULL, L, nn), tab->dct[nn * 32 + m], out);
+    for (int q = 0; q < NF / 8; ++q) {
+        const float4 a = reinterpret_cast<const float4 *>(lbuf)[q];                       // L[4q .. 4q+3]
+        const float4 b = reinterpret_cast<const float4 *>(lbuf)[NF / 4 - 1 - q];          // L[NF-4-4q .. NF-1-4q]
+        out = fmaf(fmaf(sg, b.w, a.x), tab->dct[(4 * q + 0) * 32 + li], out);
+        out = fmaf(fmaf(sg, b.z, a.y), tab->dct[(4 * q + 1) * 32 + li], out);
+        out = fmaf(fmaf(sg, b.y, a.z), tab->dct[(4 * q + 2) * 32 + li], out);
+        out = fmaf(fmaf(sg, b.x, a.w), tab->dct[(4 * q + 3) * 32 + li], out);
+    }
+    __syncwarp();
     return out;
 }
 

@@ -10,6 +10,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <cmath>
 #include <cuda_runtime.h>
 #include <atomic>
 #include <string>
@@ -25,7 +26,7 @@ namespace {
 
 constexpr int WARPS   = 8;
 constexpr int THREADS = WARPS * 32;
-constexpr int FT      = 32;                                        // frames per tile
+constexpr int FT      = 24;                                        // frames per tile
 constexpr int RAWN    = ((HOP * (FT - 1) + NFFT + 15) + 7) & ~7;   // samples per tile buffer
 constexpr int CTAS_PER_SM = 4;
 
@@ -72,6 +73,13 @@ __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// sign-extending 16-bit shared load (SASS LDS.S16; plain C++ compiles to LDS.U16 + PRMT)
+__device__ __forceinline__ int lds_s16(const int16_t *p) {
+    int v;
+    asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
+    return v;
+}
+
 // ------------------------------------------------------------------ tile geometry
 struct Tile {
     const int16_t *clip;
@@ -100,7 +108,9 @@ __device__ __forceinline__ Tile tile_geo(const RunParams &p, long long t) {
 
 // ------------------------------------------------------------------ one frame by one warp
 // pre: pre-emphasised samples of the frame in shared memory (even halfword offset).
-template <int NF>
+// TAPS: also store every stage's output (tp), the analogue of the bench collectors of
+// mfcc/core/mfcc.py:176-183; compiled out of the production instantiation.
+template <int NF, bool TAPS>
 __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, const DevTables *tab, int lane,
                                            int16_t *out, int nceptrums, const mfcc_b200_taps &tp, long long k)
 {
@@ -110,8 +120,8 @@ __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, c
 #pragma unroll
     for (int l = 0; l < 16; ++l) {
         const int n = bt + 32 * brev4(l);
-        xr[l] = ((int)pre[n] * (int)tab->curve[n]) >> 9;
-        if (tp.d_window) tp.d_window[k * NFFT + n] = (int16_t)xr[l];
+        xr[l] = (lds_s16(pre + n) * (int)tab->curve[n]) >> 9;
+        if (TAPS && tp.d_window) tp.d_window[k * NFFT + n] = (int16_t)xr[l];
     }
     int re[8], im[8];
     fft512_warp(xr, xbuf, tab, lane, re, im);
@@ -121,15 +131,15 @@ __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, c
         const int b = lane + 32 * i;
         const unsigned pw = ((unsigned)(re[i] * re[i]) + (unsigned)(im[i] * im[i])) >> 2;
         xbuf[b] = pw;
-        if (tp.d_fft) { tp.d_fft[(k * NBINS + b) * 2] = (int16_t)re[i]; tp.d_fft[(k * NBINS + b) * 2 + 1] = (int16_t)im[i]; }
-        if (tp.d_power) tp.d_power[k * NBINS + b] = pw;
+        if (TAPS && tp.d_fft) { tp.d_fft[(k * NBINS + b) * 2] = (int16_t)re[i]; tp.d_fft[(k * NBINS + b) * 2 + 1] = (int16_t)im[i]; }
+        if (TAPS && tp.d_power) tp.d_power[k * NBINS + b] = pw;
     }
     __syncwarp();
     const unsigned mel = mel_warp<NF>(xbuf, tab, lane);
-    const unsigned lg = log2fix_lane(mel);
+    const unsigned lg = log2fix_tab(mel, tab->logfrac);
     const int c = dct_warp<NF>(lg, tab, lane);
     __syncwarp();   // xbuf is rewritten by the next frame
-    if (lane < NF) {
+    if (TAPS && lane < NF) {
         if (tp.d_mel)  tp.d_mel[k * NF + lane] = (uint16_t)mel;
         if (tp.d_log2) tp.d_log2[k * NF + lane] = (uint16_t)lg;
         if (tp.d_dct)  tp.d_dct[k * NF + lane] = (int16_t)c;
@@ -157,7 +167,7 @@ __device__ __forceinline__ void issue_tile(const RunParams &p, long long t, Smem
     }
 }
 
-template <int NF>
+template <int NF, bool TAPS>
 __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const RunParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -212,7 +222,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
         int16_t *orow = static_cast<int16_t *>(p.out) + g.ci * p.out_clip_stride;
         for (int fl = warp; fl < g.nf; fl += WARPS) {
             const long long k = g.f0 + fl;
-            frame_warp<NF>(sm->pre + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
+            frame_warp<NF, TAPS>(sm->pre + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
                            orow + k * p.nceptrums, p.nceptrums, p.taps, k);
         }
         __syncthreads();
@@ -278,7 +288,7 @@ __global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
         for (int fl = warp; fl < g.nf; fl += WARPS) {
             const long long k = g.f0 + fl;
             mfccf::power_warp_f32(raw + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane);
-            const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, &sm->tab, lane);
+            const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, sm->xbuf[warp], &sm->tab, lane);
             if (lane < p.nceptrums) orow[k * p.nceptrums + lane] = c;
             __syncwarp();
         }
@@ -318,9 +328,10 @@ __global__ void k_power(const int16_t *f, uint32_t *pw, long long n_frames) {
     }
 }
 
-__global__ void k_log2(const uint16_t *m, uint16_t *o, long long total) {
+__global__ void k_log2(const uint16_t *m, uint16_t *o, long long total, const DevTables *tab) {
+    // through the same table as the fused kernel (read from global memory here)
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
-        o[i] = (uint16_t)log2fix_lane(m[i]);
+        o[i] = (uint16_t)log2fix_tab(m[i], tab->logfrac);
 }
 
 struct StageSmem {
@@ -426,7 +437,7 @@ __global__ void __launch_bounds__(THREADS) mfcc_int_step(int16_t *state, const i
             const int i = lane + 32 * r;
             if (i <= HIST) st[i] = nv[r];
         }
-        frame_warp<NF>(pre, sm->xbuf[warp], &sm->tab, lane, out + (long long)s * nceptrums, nceptrums, none, 0);
+        frame_warp<NF, false>(pre, sm->xbuf[warp], &sm->tab, lane, out + (long long)s * nceptrums, nceptrums, none, 0);
         __syncwarp();
     }
 }
@@ -465,7 +476,7 @@ __global__ void __launch_bounds__(THREADS) mfcc_f32_step(int16_t *state, const i
         // new state = raw(HOP-1 .. 511)
         for (int i = lane; i <= HIST; i += 32) st[i] = raw[2 + i + HOP - 1];
         mfccf::power_warp_f32(raw + 2, sm->xbuf[warp], &sm->tab, lane);
-        const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, &sm->tab, lane);
+        const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, sm->xbuf[warp], &sm->tab, lane);
         if (lane < nceptrums) out[(long long)s * nceptrums + lane] = c;
         __syncwarp();
     }
@@ -544,22 +555,35 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
     for (int n = 0; n < NFFT; ++n) {
         if (c.window_curve[n] < 0 || c.window_curve[n] > 511)
             return fail(MFCC_B200_EUNSUPPORTED, "window_curve out of the 9-bit range");
-        t.curve[n] = (int16_t)c.window_curve[n];
+        t.curve[n] = (uint16_t)c.window_curve[n];
     }
     int g = 0, first = 0;
+    const int maxseg = (c.nfilters == 32) ? 21 : 42;
     for (int b = 0; b < NBINS; ++b) {
         if (c.mel_weight[b] >> 30) return fail(MFCC_B200_EUNSUPPORTED, "mel_weight wider than 30 bits");
-        t.melw[b] = c.mel_weight[b];
         if (c.mel_close[b]) {
             if (g >= 40) return fail(MFCC_B200_EUNSUPPORTED, "too many mel segments");
             t.seg_first[g] = (int16_t)first;
             t.seg_close[g] = (int16_t)b;
+            const int len = b - first + 1;
+            if (g == 0) {
+                if (len > 4) return fail(MFCC_B200_EUNSUPPORTED, "first mel segment longer than 4 bins");
+                for (int j = 0; j < len; ++j) t.seg0_wa[j] = (first + j == b) ? (1u << 30) : c.mel_weight[first + j];
+            } else {
+                if (len > maxseg || g > c.nfilters) return fail(MFCC_B200_EUNSUPPORTED, "mel segment too long for the kernel's table");
+                for (int j = 0; j < len; ++j) {
+                    const bool closing = (first + j == b);
+                    const uint32_t w = c.mel_weight[first + j];
+                    t.melab[j * c.nfilters + (g - 1)] = closing ? make_uint2(1u << 30, 0u) : make_uint2(w, (1u << 30) - w);
+                }
+            }
             first = b + 1;
             ++g;
         }
     }
     if (g != c.nfilters + 1 || first != NBINS)
         return fail(MFCC_B200_EUNSUPPORTED, "mel tables must describe nfilters+1 segments ending at the last bin");
+    for (int z = 0; z < 2048; ++z) t.logfrac[z] = (uint16_t)log2fix_frac(2048u + z);
     t.nseg = g;
     t.mel_lo_bit = c.mel_lo_bit;
     if (build_dct_plan(c.nfilters, c.tw_dct, t) != 0)
@@ -570,27 +594,76 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
 int build_tables_f(const mfcc_b200_cfg &c, mfccf::DevTablesF &t) {
     memset(&t, 0, sizeof(t));
     const double PI = 3.14159265358979323846;
-    const int nf = c.nfilters;
+    const int nf = c.nfilters, nb = mfccf::NBINS1;
+    const int maxseg = (nf == 32) ? 21 : 42;
     for (int n = 0; n < NFFT; ++n) t.window[n] = c.f_window[n] * (1.0f / 32.0f);   // see emph_win()
-    for (int k = 0; k < 256; ++k)
-        t.tw256[k] = make_float2((float)cos(2 * PI * k / 256), (float)-sin(2 * PI * k / 256));
+    for (int k1 = 0; k1 < 8; ++k1)
+        for (int l = 0; l < 32; ++l)
+            t.twA[k1 * 32 + l] = make_float2((float)cos(2 * PI * (l * k1) / 256), (float)-sin(2 * PI * (l * k1) / 256));
+    for (int p = 0; p < 8; ++p)
+        for (int cc = 0; cc < 4; ++cc)
+            t.twB[p * 4 + cc] = make_float2((float)cos(2 * PI * (cc * p) / 32), (float)-sin(2 * PI * (cc * p) / 32));
     for (int k = 0; k <= 128; ++k)
         t.tw512[k] = make_float2((float)cos(2 * PI * k / 512), (float)-sin(2 * PI * k / 512));
+    // DCT: the kernel uses D[k][nf-1-n] = (-1)^k D[k][n]; check it on the matrix we were given
     for (int k = 0; k < nf; ++k)
-        for (int n = 0; n < nf; ++n) t.dct[n * 32 + k] = c.f_dct[k * nf + n];
-    int off = 0;
-    for (int m = 0; m < nf; ++m) {
-        const float *row = c.f_mel + (size_t)m * mfccf::NBINS1;
-        int lo = 0, hi = mfccf::NBINS1;
-        while (lo < hi && row[lo] == 0.0f) ++lo;
-        while (hi > lo && row[hi - 1] == 0.0f) --hi;
-        if (off + (hi - lo) > mfccf::MELW_MAX)
-            return fail(MFCC_B200_EUNSUPPORTED, "f_mel is too dense for the sparse filter table");
-        t.mel_lo[m] = (int16_t)lo; t.mel_n[m] = (int16_t)(hi - lo); t.mel_off[m] = (int16_t)off;
-        for (int b = lo; b < hi; ++b) t.melw[off++] = row[b];
+        for (int n = 0; n < nf / 2; ++n) {
+            const float a = c.f_dct[k * nf + n], b = c.f_dct[k * nf + nf - 1 - n];
+            if (fabsf(((k & 1) ? -b : b) - a) > 1e-6f)
+                return fail(MFCC_B200_EUNSUPPORTED, "f_dct is not a DCT-II matrix (mirror symmetry missing)");
+            t.dct[n * 32 + k] = a;
+        }
+    // Mel: every bin may feed two consecutive filters.  Segment g holds the bins whose
+    // filters are {g-1, g}; its bins get the rise weight of g and the fall weight of g-1.
+    std::vector<int> seg(nb);
+    int cur = 0;
+    for (int b = 0; b < nb; ++b) {
+        int lo = -1, hi = -1;
+        for (int m = 0; m < nf; ++m)
+            if (c.f_mel[(size_t)m * nb + b] != 0.0f) { if (lo < 0) lo = m; hi = m; }
+        int g = cur;
+        if (lo >= 0) {
+            if (hi - lo > 1) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: a bin feeds more than two consecutive filters");
+            if (hi > lo) g = hi;
+            else {
+                // one filter only: on its falling side (weight going down, or already in
+                // the next segment) the bin belongs to segment lo+1, else to segment lo
+                const bool falling = b > 0 && c.f_mel[(size_t)lo * nb + b] < c.f_mel[(size_t)lo * nb + b - 1];
+                g = (falling || cur == lo + 1) ? lo + 1 : (cur > lo ? cur : lo);
+            }
+            if (g < cur || g > lo + 1) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: filters are not ordered triangles");
+        }
+        seg[b] = cur = g;
     }
+    if (cur > nf) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: too many segments");
+    // padded layout: segment g (lane g-1) starts at an address whose bank no other
+    // segment start uses, so the lanes' walks never collide
+    std::vector<int> first(nf + 2, -1), len(nf + 2, 0), base(nf + 2, 0);
+    for (int b = 0; b < nb; ++b) { if (first[seg[b]] < 0) first[seg[b]] = b; ++len[seg[b]]; }
+    if (len[0] > 4) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: first segment longer than 4 bins");
+    bool used[32] = {false};
+    int next = len[0];
+    for (int g = 1; g <= nf; ++g) {
+        if (len[g] > maxseg) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: segment too long for the kernel's table");
+        int a = next;
+        const int nlanes = (nf == 32) ? 32 : 16;
+        while (used[a % nlanes]) ++a;
+        used[a % nlanes] = true;
+        base[g] = a;
+        next = a + len[g];
+        t.seg_base[g - 1] = (uint16_t)a;
+    }
+    if (next + maxseg > mfccf::PW_WORDS) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: padded power layout does not fit");
+    for (int b = 0; b < nb; ++b) {
+        const int g = seg[b], j = b - first[g];
+        t.paddr[b] = (uint16_t)(base[g] + j);
+        const float rise = (g < nf) ? c.f_mel[(size_t)g * nb + b] : 0.0f;
+        const float fall = (g >= 1) ? c.f_mel[(size_t)(g - 1) * nb + b] : 0.0f;
+        if (g == 0) t.seg0w[j] = rise;
+        else t.melw[j * nf + (g - 1)] = make_float2(rise, fall);
+    }
+    for (int j = len[0]; j < 4; ++j) t.seg0w[j] = 0.0f;     // paddr[j] of a later segment, weight 0
     t.mel_floor = c.f_mel_floor > 0.0f ? c.f_mel_floor : 0.0f;
-    (void)c.f_preemph;
     return MFCC_B200_OK;
 }
 
@@ -670,8 +743,10 @@ int mfcc_b200_create(const mfcc_b200_cfg *cfg, void **handle)
         delete h;
         return fail(MFCC_B200_ECUDA, std::string("mfcc_b200_create: ") + cudaGetErrorString(e));
     }
-    rc = set_smem(mfcc_int_fused<32>, sizeof(Smem));
-    if (!rc) rc = set_smem(mfcc_int_fused<16>, sizeof(Smem));
+    rc = set_smem(mfcc_int_fused<32, false>, sizeof(Smem));
+    if (!rc) rc = set_smem(mfcc_int_fused<16, false>, sizeof(Smem));
+    if (!rc) rc = set_smem(mfcc_int_fused<32, true>, sizeof(Smem));
+    if (!rc) rc = set_smem(mfcc_int_fused<16, true>, sizeof(Smem));
     if (!rc) rc = set_smem(mfcc_int_step<32>, sizeof(StepSmem));
     if (!rc) rc = set_smem(mfcc_int_step<16>, sizeof(StepSmem));
     if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_FFT, 32>, sizeof(StageSmem));
@@ -733,8 +808,11 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
         if (h->cfg.nfilters == 32) mfcc_f32_fused<32><<<(unsigned)grid, THREADS, sizeof(SmemF), s>>>(p);
         else                       mfcc_f32_fused<16><<<(unsigned)grid, THREADS, sizeof(SmemF), s>>>(p);
     } else {
-        if (h->cfg.nfilters == 32) mfcc_int_fused<32><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
-        else                       mfcc_int_fused<16><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+        const bool nf32 = h->cfg.nfilters == 32;
+        if (taps && nf32)  mfcc_int_fused<32, true><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+        else if (taps)     mfcc_int_fused<16, true><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+        else if (nf32)     mfcc_int_fused<32, false><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+        else               mfcc_int_fused<16, false><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
     }
     g_launches.fetch_add(1);
     CUDA_TRY(cudaGetLastError());
@@ -824,7 +902,7 @@ int mfcc_b200_stage(void *handle, int32_t stage, const void *d_in, void *d_out, 
         k_power<<<grid_1d(n * NBINS, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (uint32_t *)d_out, n);
         break;
     case MFCC_B200_STAGE_LOG2:
-        k_log2<<<grid_1d(n * nf, B, h->sm_count), B, 0, s>>>((const uint16_t *)d_in, (uint16_t *)d_out, n * nf);
+        k_log2<<<grid_1d(n * nf, B, h->sm_count), B, 0, s>>>((const uint16_t *)d_in, (uint16_t *)d_out, n * nf, h->d_tab);
         break;
     default: {
         const int grid = grid_1d(n, WARPS, h->sm_count);
