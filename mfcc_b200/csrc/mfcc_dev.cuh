@@ -25,12 +25,12 @@ struct alignas(16) DevTables {
     int2     twB[128];       // stages 4..7, doubled (2re, 2im): [16 | 16 | 32 | 64] entries
     int2     tw8[256];       // stage 8, doubled, natural order
     uint2    melab[672];     // FilterBank weights, padded per segment: see mel_warp()
-    uint32_t seg0_wa[4];     // segment 0 (feeds filter 0 only)
+    uint32_t pad0[4];
     uint16_t logfrac[2048];  // Log2Fix fraction bits 10..1 for every 12-bit mantissa: see log2fix_tab()
     int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
     int2     dct_twf[32];    // final DCT stage, lane j = bin j, doubled
     uint16_t curve[512];     // window multipliers (9 bits, unsigned), window.py:59-115
-    int16_t  seg_first[40];  // first bin of mel segment g
+    int16_t  seg_walk[40];   // first bin of lane's walk: segment lane+1 (lane 0: segments 0 and 1)
     int16_t  seg_close[40];  // closing bin of mel segment g
     int32_t  mel_lo_bit;     // filterbank.py:122
     int32_t  nseg;
@@ -256,7 +256,7 @@ __device__ __forceinline__ unsigned mel_warp(const unsigned *pw, const DevTables
 {
     constexpr int MAXSEG = (NF == 32) ? 21 : 42;
     const int li = lane & (NF - 1);
-    const unsigned *p = pw + tab->seg_first[li + 1];
+    const unsigned *p = pw + tab->seg_walk[li];
     unsigned long long a = 0, b = 0;
     if (NF == 32) {
 #pragma unroll
@@ -279,12 +279,11 @@ __device__ __forceinline__ unsigned mel_warp(const unsigned *pw, const DevTables
         a += __shfl_xor_sync(FULL, a, 16);
         b += __shfl_xor_sync(FULL, b, 16);
     }
-    // segment 0 (its own output is suppressed, filterbank.py:139) feeds filter 0
-    unsigned long long a0 = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) a0 += (unsigned long long)pw[j] * tab->seg0_wa[j];
+    // Lane 0 walks segment 0 too (its own output is suppressed, filterbank.py:139, but
+    // Abar_0 feeds filter 0): those bins carry wa in the wb slot, so b already holds
+    // Abar_0 + Bbar_1 and nothing comes from a neighbour.
     unsigned long long pa = __shfl_up_sync(FULL, a, 1);
-    if (li == 0) pa = a0;
+    if (li == 0) pa = 0;
     const unsigned long long x = pa + b;
     return (unsigned)(x >> tab->mel_lo_bit) & 0xffffu;
 }

@@ -30,7 +30,6 @@ struct alignas(16) DevTablesF {
     float2 tw512[132];                 // exp(-2 pi i k / 512), k = 0..128
     float  dct[16 * 32];               // dct[n * 32 + k] = D[k][n], n < nfilters / 2 (the rest by symmetry)
     float2 melw[672];                  // [step][lane] (rise weight, fall weight) of the lane's segment
-    float  seg0w[4];                   // rise weights of segment 0 (filter 0)
     uint16_t paddr[264];               // word address of bin b in the padded power area
     uint16_t seg_base[32];             // address of the first bin of lane's segment (segment lane+1)
     float  mel_floor;                  // energies are clamped to this before log2 (0 = off)
@@ -202,11 +201,10 @@ __device__ __forceinline__ float cepstrum_warp_f32(float *pw, float *lbuf, const
         u += __shfl_xor_sync(FULL, u, 16);
         v += __shfl_xor_sync(FULL, v, 16);
     }
-    float u0 = 0.0f;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) u0 = fmaf(pw[tab->paddr[j]], tab->seg0w[j], u0);
+    // lane 0 walks segment 0 as well (its rise weights sit in the fall slot: both feed
+    // filter 0), so it takes nothing from a neighbour
     float up = __shfl_up_sync(FULL, u, 1);
-    if (li == 0) up = u0;
+    if (li == 0) up = 0.0f;
     const float L = __log2f(fmaxf(up + v, tab->mel_floor));
     // orthonormal DCT-II with D[k][NF-1-n] = (-1)^k D[k][n]: NF/2 multiply-adds per lane
     lbuf[lane] = L;

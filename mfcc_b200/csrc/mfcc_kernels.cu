@@ -557,25 +557,26 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
             return fail(MFCC_B200_EUNSUPPORTED, "window_curve out of the 9-bit range");
         t.curve[n] = (uint16_t)c.window_curve[n];
     }
-    int g = 0, first = 0;
+    int g = 0, first = 0, seg0_len = 0;
     const int maxseg = (c.nfilters == 32) ? 21 : 42;
     for (int b = 0; b < NBINS; ++b) {
         if (c.mel_weight[b] >> 30) return fail(MFCC_B200_EUNSUPPORTED, "mel_weight wider than 30 bits");
         if (c.mel_close[b]) {
             if (g >= 40) return fail(MFCC_B200_EUNSUPPORTED, "too many mel segments");
-            t.seg_first[g] = (int16_t)first;
             t.seg_close[g] = (int16_t)b;
             const int len = b - first + 1;
-            if (g == 0) {
-                if (len > 4) return fail(MFCC_B200_EUNSUPPORTED, "first mel segment longer than 4 bins");
-                for (int j = 0; j < len; ++j) t.seg0_wa[j] = (first + j == b) ? (1u << 30) : c.mel_weight[first + j];
-            } else {
-                if (len > maxseg || g > c.nfilters) return fail(MFCC_B200_EUNSUPPORTED, "mel segment too long for the kernel's table");
-                for (int j = 0; j < len; ++j) {
-                    const bool closing = (first + j == b);
-                    const uint32_t w = c.mel_weight[first + j];
-                    t.melab[j * c.nfilters + (g - 1)] = closing ? make_uint2(1u << 30, 0u) : make_uint2(w, (1u << 30) - w);
-                }
+            // lane g-1 walks segment g; lane 0 starts at bin 0 and takes segment 0 first,
+            // with its wa weights in the wb slot (both end up in filter 0)
+            const int lane_of = g == 0 ? 0 : g - 1;
+            const int j0 = g == 1 ? seg0_len : 0;
+            if (g == 0) seg0_len = len;
+            else t.seg_walk[g - 1] = (int16_t)(g == 1 ? 0 : first);
+            if (j0 + len > maxseg || g > c.nfilters) return fail(MFCC_B200_EUNSUPPORTED, "mel segment too long for the kernel's table");
+            for (int j = 0; j < len; ++j) {
+                const bool closing = (first + j == b);
+                const uint32_t w = c.mel_weight[first + j];
+                const uint32_t wa = closing ? (1u << 30) : w, wb = closing ? 0u : (1u << 30) - w;
+                t.melab[(j0 + j) * c.nfilters + lane_of] = g == 0 ? make_uint2(0u, wa) : make_uint2(wa, wb);
             }
             first = b + 1;
             ++g;
@@ -640,18 +641,21 @@ int build_tables_f(const mfcc_b200_cfg &c, mfccf::DevTablesF &t) {
     // segment start uses, so the lanes' walks never collide
     std::vector<int> first(nf + 2, -1), len(nf + 2, 0), base(nf + 2, 0);
     for (int b = 0; b < nb; ++b) { if (first[seg[b]] < 0) first[seg[b]] = b; ++len[seg[b]]; }
-    if (len[0] > 4) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: first segment longer than 4 bins");
     bool used[32] = {false};
-    int next = len[0];
-    for (int g = 1; g <= nf; ++g) {
-        if (len[g] > maxseg) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: segment too long for the kernel's table");
+    int next = 0;
+    const int nlanes = (nf == 32) ? 32 : 16;
+    for (int g = 0; g <= nf; ++g) {
+        // lane g-1 walks segment g; lane 0 walks segments 0 and 1 back to back
+        if ((g <= 1 ? len[0] + len[1] : len[g]) > maxseg)
+            return fail(MFCC_B200_EUNSUPPORTED, "f_mel: segment too long for the kernel's table");
         int a = next;
-        const int nlanes = (nf == 32) ? 32 : 16;
-        while (used[a % nlanes]) ++a;
-        used[a % nlanes] = true;
+        if (g != 1) {
+            while (used[a % nlanes]) ++a;
+            used[a % nlanes] = true;
+        }
         base[g] = a;
         next = a + len[g];
-        t.seg_base[g - 1] = (uint16_t)a;
+        if (g != 1) t.seg_base[g == 0 ? 0 : g - 1] = (uint16_t)a;
     }
     if (next + maxseg > mfccf::PW_WORDS) return fail(MFCC_B200_EUNSUPPORTED, "f_mel: padded power layout does not fit");
     for (int b = 0; b < nb; ++b) {
@@ -659,10 +663,9 @@ int build_tables_f(const mfcc_b200_cfg &c, mfccf::DevTablesF &t) {
         t.paddr[b] = (uint16_t)(base[g] + j);
         const float rise = (g < nf) ? c.f_mel[(size_t)g * nb + b] : 0.0f;
         const float fall = (g >= 1) ? c.f_mel[(size_t)(g - 1) * nb + b] : 0.0f;
-        if (g == 0) t.seg0w[j] = rise;
-        else t.melw[j * nf + (g - 1)] = make_float2(rise, fall);
+        if (g == 0) t.melw[j * nf + 0] = make_float2(0.0f, rise);              // rise of filter 0, in the fall slot
+        else t.melw[((g == 1 ? len[0] : 0) + j) * nf + (g - 1)] = make_float2(rise, fall);
     }
-    for (int j = len[0]; j < 4; ++j) t.seg0w[j] = 0.0f;     // paddr[j] of a later segment, weight 0
     t.mel_floor = c.f_mel_floor > 0.0f ? c.f_mel_floor : 0.0f;
     return MFCC_B200_OK;
 }

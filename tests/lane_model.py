@@ -140,28 +140,83 @@ def fft512_frame(w, tw):
     return re, im, conflicts
 
 
-def mel_lanes(pw, nfilters, samplerate=16e3, nfft=512, lo_bit=31):
-    """Lane g' sums segment g'+off; neighbours exchange (A, peak) by shuffle."""
+def bf1_rr(x0, x1):
+    """kernel's W^0 butterfly on real operands (mfcc_dev.cuh: bf1_rr)."""
+    return (x0 + x1) >> 1, (x0 - x1) >> 1
+
+
+def bfj_cc(x0r, x0i, x1r, x1i):
+    """kernel's -j butterfly (mfcc_dev.cuh: bfj_cc / bfj_rr with x0i = x1i = 0)."""
+    tr, ti = x1i, -x1r
+    return (x0r + tr) >> 1, (x0i + ti) >> 1, (x0r - tr) >> 1, (x0i - ti) >> 1
+
+
+def mel_tables(nfilters, samplerate=16e3, nfft=512):
+    """What mfcc_b200_create() builds for mel_warp(): per lane (segment lane+1) and step
+    the weight pair (wa, wb), zero past the segment's end; segment 0 separately."""
     w, seg, close = T.mel_weights(nfilters, nfft, samplerate)
     bounds = T.mel_segment_bounds(nfilters, nfft, samplerate)
-    nseg = len(bounds)
-    assert nseg == nfilters + 1
+    maxseg = 21 if nfilters == 32 else 42
+    assert len(bounds) == nfilters + 1
+    ab = np.zeros((maxseg, nfilters, 2), dtype=np.int64)
+    len0 = bounds[0][1] - bounds[0][0] + 1
+    for g, (first, cl) in enumerate(bounds):
+        n = cl - first + 1
+        j0 = len0 if g == 1 else 0
+        assert j0 + n <= maxseg
+        for j in range(n):
+            closing = first + j == cl
+            wa = (1 << 30) if closing else int(w[first + j])
+            wb = 0 if closing else (1 << 30) - int(w[first + j])
+            if g == 0:
+                ab[j, 0] = (0, wa)           # Abar_0 feeds filter 0: kept in lane 0's wb slot
+            else:
+                ab[j0 + j, g - 1] = (wa, wb)
+    return ab, bounds
+
+
+def mel_lanes(pw, nfilters, samplerate=16e3, nfft=512, lo_bit=31):
+    """Lane g-1 walks segment g (lane 0: segments 0 and 1) with two 64-bit multiply-adds
+    per step (fixed trip count, zero-padded weights); filter g-1 = Abar_{g-1} (from the
+    neighbour) + Bbar_g."""
+    ab, bounds = mel_tables(nfilters, samplerate, nfft)
+    maxseg = ab.shape[0]
     M64 = (1 << 64) - 1
-    A = [0] * nseg
-    D = [0] * nseg
-    PK = [0] * nseg
-    for g in range(nseg):
-        first, cl = bounds[g]
-        for b in range(first, cl):
-            A[g] = (A[g] + int(pw[b]) * int(w[b])) & M64
-            D[g] = (D[g] + int(pw[b])) & 0xFFFFFFFF
-        PK[g] = int(pw[cl])
+    pwx = np.concatenate([np.asarray(pw, dtype=np.int64), np.full(maxseg + 8, 12345)])   # readable overrun
+    a = [0] * nfilters
+    b = [0] * nfilters
+    for li in range(nfilters):
+        first = 0 if li == 0 else bounds[li + 1][0]
+        for j in range(maxseg):
+            d = int(pwx[first + j])
+            a[li] = (a[li] + d * int(ab[j, li, 0])) & M64
+            b[li] = (b[li] + d * int(ab[j, li, 1])) & M64
     out = np.zeros(nfilters, dtype=np.int64)
-    for g in range(1, nseg):
-        e = (PK[g - 1] + D[g]) & 0xFFFFFFFF
-        x = (A[g - 1] - A[g] + (e << 30)) & M64
-        out[g - 1] = (x >> lo_bit) & 0xFFFF
+    for li in range(nfilters):
+        pa = 0 if li == 0 else a[li - 1]                   # shuffle up
+        out[li] = (((pa + b[li]) & M64) >> lo_bit) & 0xFFFF
     return out
+
+
+def log2_table():
+    """logfrac[] of DevTables: the ten squarings for every 12-bit mantissa."""
+    t = np.zeros(2048, dtype=np.int64)
+    for z0 in range(2048, 4096):
+        z, frac = z0, 0
+        for _ in range(10):
+            c = z * z
+            bit = (c >> 23) & 1
+            z = c >> (11 + bit)
+            frac = (frac << 1) | bit
+        t[z0 - 2048] = frac
+    return t
+
+
+def log2_tab_lane(m, table):
+    mm = max(int(m), 1)
+    sh = mm.bit_length() - 1
+    z = (mm << 11) >> sh
+    return ((sh << 11) + (int(table[z - 2048]) << 1)) & 0x7FFF
 
 
 def log2_lane(m, prec=11):

@@ -49,3 +49,26 @@ def test_log2_lane_all_values():
     want = R.log2fix(m[::17], 16, 15)
     got = np.array([LM.log2_lane(v) for v in m[::17]])
     assert np.array_equal(got, want)
+
+
+def test_trivial_butterflies_equal_the_general_one():
+    """bf1_rr / bfj_* (used for W^0 and -j in stages 0-3) are the general butterfly with
+    those twiddles, for every combination of extreme and random 16-bit operands."""
+    rng = np.random.default_rng(3)
+    edge = np.array([-32768, -32767, -1, 0, 1, 2, 32766, 32767])
+    v = np.concatenate([edge, rng.integers(-32768, 32768, 200)])
+    x0r, x0i, x1r, x1i = [a.ravel() for a in np.meshgrid(v[:24], v[:24], v[:24], v[:24])]
+    z = np.zeros_like(x0r)
+    a, b, c, d = LM.bfly(x0r, z, x1r, z, 16384, 0)
+    y0, y1 = LM.bf1_rr(x0r, x1r)
+    assert np.array_equal(a, y0) and np.array_equal(c, y1) and not b.any() and not d.any()
+    want = LM.bfly(x0r, x0i, x1r, x1i, 0, -16384)
+    got = LM.bfj_cc(x0r, x0i, x1r, x1i)
+    for w_, g_ in zip(want, got):
+        assert np.array_equal(w_, LM.s16(g_)) and np.array_equal(g_, LM.s16(g_))
+
+
+def test_log2_table_equals_the_loop():
+    t = LM.log2_table()
+    for m in list(range(0, 4200)) + list(range(60000, 65536)) + [32767, 32768, 16384, 9999]:
+        assert LM.log2_tab_lane(m, t) == LM.log2_lane(m)
