@@ -147,6 +147,45 @@ int  mfcc_b200_state_bytes(void *handle, int32_t n_streams, int64_t *bytes);
 int  mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n_streams,
                     void *d_out, void *stream);
 
+/*
+ * ---- the steps after the path in the reference's tool chain ----
+ * All buffers are device pointers owned by the caller.
+ *
+ * Cepstral lifter, software/lift.py:12-26, :38-39:
+ *   d_out[r][n] = int16( d_lift[n] * d_in[r][n] ), float64 product, truncation toward zero
+ *   like ndarray.astype(np.int16); d_lift[n] = 1 + (L/2) sin(pi n / L), L = 22 in the script.
+ */
+int  mfcc_b200_lifter(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t ncoeff,
+                      const double *d_lift, void *stream);
+
+/*
+ * Per-coefficient standardisation over time, sklearn.preprocessing.scale(spec, axis=1)
+ * followed by astype(np.int16) (software/genlibrosa.py:25-28), for n_clips matrices
+ * [n_frames][ncoeff] of int16 (in_is_float = 0) or float32 (in_is_float = 1).
+ */
+int  mfcc_b200_standardize(const void *d_in, int32_t in_is_float, int16_t *d_out, int64_t n_frames,
+                           int32_t ncoeff, int32_t n_clips, void *stream);
+
+/*
+ * Serial framing of cepstrum columns, MagicInserter (mfcc/misc/magic.py:27-39) and the
+ * byte order of the UART sender (mfcc/targets/mic2mfcc.py:58-62); what
+ * cepstrum_get_column() parses (software/cepstrum.c:15-68): per column the 16-bit magic
+ * (0xa55a) then ncoeff words, high byte first.  d_bytes holds n_cols * (ncoeff+1) * 2 bytes.
+ */
+int  mfcc_b200_uart_frame(const int16_t *d_cols, uint8_t *d_bytes, int64_t n_cols, int32_t ncoeff,
+                          uint32_t magic, void *stream);
+
+/*
+ * Voice-activity gate of the host (software/cepstrum.c:13, :93-183), one step per new
+ * column per stream: d_ring [n_streams][window] int16 keeps the last `window` (93 in
+ * software/recv.c:17-18) values of coefficient 0, d_head [n_streams] the ring position;
+ * d_power gets cepstrum_eval_power()'s sum (C int, wraps), d_active = power >= threshold
+ * (POWER_THRESHOLD = 100000000).  Zero-initialised state = a ring of silence.
+ */
+int  mfcc_b200_vad_step(int16_t *d_ring, int32_t *d_head, const int16_t *d_cols, int32_t n_streams,
+                        int32_t ncoeff, int32_t window, int32_t threshold, int32_t *d_power,
+                        uint8_t *d_active, void *stream);
+
 /* Number of kernels this library has launched since it was loaded (bench.py's
  * gpu_launches). */
 int64_t     mfcc_b200_launch_count(void);

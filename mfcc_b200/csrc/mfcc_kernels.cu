@@ -263,6 +263,10 @@ __global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
         int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
         for (int i = tid; i < (int)(sizeof(mfccf::DevTablesF) / 16); i += THREADS) dst[i] = src[i];
     }
+    // The padded power area has gaps no frame ever writes; the mel walk reads them with
+    // zero weights, so they must hold finite numbers (0 * NaN would poison the sum).
+    for (int i = tid; i < WARPS * mfccf::PW_WORDS; i += THREADS)
+        sm->xbuf[i / mfccf::PW_WORDS][mfccf::PW_OFF + i % mfccf::PW_WORDS] = 0.0f;
     if (tid == 0) { mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1); }
     __syncthreads();
 
@@ -461,6 +465,8 @@ __global__ void __launch_bounds__(THREADS) mfcc_f32_step(int16_t *state, const i
         int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
         for (int i = tid; i < (int)(sizeof(mfccf::DevTablesF) / 16); i += THREADS) dst[i] = src[i];
     }
+    for (int i = tid; i < WARPS * mfccf::PW_WORDS; i += THREADS)      // see mfcc_f32_fused
+        sm->xbuf[i / mfccf::PW_WORDS][mfccf::PW_OFF + i % mfccf::PW_WORDS] = 0.0f;
     __syncthreads();
     constexpr int HIST = NFFT - HOP;                      // 342
     for (int s = blockIdx.x * WARPS + warp; s < n_streams; s += gridDim.x * WARPS) {
@@ -689,6 +695,12 @@ inline int grid_1d(long long total, int block, int sm_count) {
 }
 
 }  // namespace
+
+// shared with mfcc_post.cu
+namespace mfccb_host {
+int fail_ext(int code, const char *msg) { return fail(code, msg); }
+void count_launch() { g_launches.fetch_add(1); }
+}  // namespace mfccb_host
 
 // =================================================================== C ABI
 extern "C" {

@@ -1,0 +1,184 @@
+// Post-processing and live-stream helpers of the B200 MFCC path (include/mfcc_b200.h,
+// "next rows" f2 and f3 of SURVEY.md 8(f)): the cepstral lifter and the per-coefficient
+// standardisation the reference's scripts apply to the cepstra, the UART column framing
+// of the microphone build and the host's voice-activity gate.  All of them are
+// element-wise or tiny per-stream reductions: HBM-bound by construction.
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/mfcc_b200.h"
+
+namespace mfccb_host {
+int fail_ext(int code, const char *msg);
+void count_launch();
+}
+using mfccb_host::fail_ext;
+
+namespace {
+
+__device__ __forceinline__ int16_t trunc16(double v) {
+    // ndarray.astype(np.int16) on float64: truncate toward zero, keep the low 16 bits
+    return (int16_t)(long long)v;
+}
+
+// software/lift.py:12-26, :38-39: out = int16(lift[n] * c), float64 product
+__global__ void k_lifter(const int16_t *in, int16_t *out, long long total, int ncoeff, const double *lift) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+        out[i] = trunc16(lift[i % ncoeff] * (double)in[i]);
+}
+
+// sklearn.preprocessing.scale over time, per clip and coefficient (software/genlibrosa.py:25-28):
+// one CTA per (clip, coefficient) column; mean, then centred second moment, in float64.
+template <typename T>
+__global__ void k_standardize(const T *in, int16_t *out, long long n_frames, int ncoeff, long long clip_stride) {
+    const int clip = blockIdx.y, c = blockIdx.x;
+    const T *src = in + (long long)clip * clip_stride + c;
+    int16_t *dst = out + (long long)clip * clip_stride + c;
+    __shared__ double red[32];
+    __shared__ double s_mean, s_std;
+    auto block_sum = [&](double v) {
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+        __syncthreads();
+        double t = 0.0;
+        if (threadIdx.x < 32) {
+            t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+            for (int o = 16; o; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        }
+        __syncthreads();
+        return t;                       // valid in warp 0
+    };
+    double acc = 0.0;
+    for (long long k = threadIdx.x; k < n_frames; k += blockDim.x) acc += (double)src[k * ncoeff];
+    double tot = block_sum(acc);
+    if (threadIdx.x == 0) s_mean = tot / (double)n_frames;
+    __syncthreads();
+    const double mean = s_mean;
+    acc = 0.0;
+    for (long long k = threadIdx.x; k < n_frames; k += blockDim.x) {
+        const double d = (double)src[k * ncoeff] - mean;
+        acc += d * d;
+    }
+    tot = block_sum(acc);
+    if (threadIdx.x == 0) {
+        const double sd = sqrt(tot / (double)n_frames);
+        s_std = sd < 10.0 * 2.220446049250313e-16 ? 1.0 : sd;     // _handle_zeros_in_scale
+    }
+    __syncthreads();
+    const double sd = s_std;
+    for (long long k = threadIdx.x; k < n_frames; k += blockDim.x)
+        dst[k * ncoeff] = trunc16(((double)src[k * ncoeff] - mean) / sd);
+}
+
+// mfcc/misc/magic.py:27-39 + mfcc/targets/mic2mfcc.py:58-62: magic word, then the
+// coefficients, every 16-bit word high byte first
+__global__ void k_uart_frame(const int16_t *cols, uint8_t *bytes, long long n_cols, int ncoeff, unsigned magic) {
+    const long long words = n_cols * (ncoeff + 1);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < words; i += (long long)gridDim.x * blockDim.x) {
+        const long long col = i / (ncoeff + 1);
+        const int j = (int)(i - col * (ncoeff + 1));
+        const unsigned w = j == 0 ? magic : (unsigned)(uint16_t)cols[col * ncoeff + j - 1];
+        bytes[2 * i] = (uint8_t)(w >> 8);
+        bytes[2 * i + 1] = (uint8_t)w;
+    }
+}
+
+// software/cepstrum.c:93-183.  Per stream a ring of the last `window` values of
+// coefficient 0 (the host keeps whole columns; only c0 is ever summed).  head = next
+// write position = oldest column.  After the new column is stored, power = sum of c0^2
+// over the columns the host's loop visits: ring elements i in [size/3, 2*size/3) step
+// ncoeff of a ring of size = window * ncoeff, i.e. columns ceil((size/3)/ncoeff) ..
+// relative to the oldest.  C `int` arithmetic: wraps modulo 2^32.
+__global__ void k_vad_step(int16_t *ring, int *head, const int16_t *cols, int n_streams, int ncoeff, int window,
+                           int first_col, int last_col, int threshold, int *power, uint8_t *active) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_streams) return;
+    int16_t *r = ring + (long long)s * window;
+    int h = head[s];
+    r[h] = cols[(long long)s * ncoeff];
+    h = h + 1 == window ? 0 : h + 1;
+    head[s] = h;
+    unsigned p = 0;
+    for (int c = first_col; c < last_col; ++c) {
+        int idx = h + c;
+        if (idx >= window) idx -= window;
+        const int v = r[idx];
+        p += (unsigned)(v * v);
+    }
+    power[s] = (int)p;
+    active[s] = (int)p >= threshold;
+}
+
+inline int grid_for(long long total, int block) {
+    long long g = (total + block - 1) / block;
+    if (g > 148 * 16) g = 148 * 16;
+    return g < 1 ? 1 : (int)g;
+}
+
+#define POST_LAUNCH_CHECK()                                                          \
+    do {                                                                             \
+        mfccb_host::count_launch();                                                  \
+        cudaError_t e_ = cudaGetLastError();                                         \
+        if (e_ != cudaSuccess) return fail_ext(MFCC_B200_ECUDA, cudaGetErrorString(e_)); \
+    } while (0)
+
+}  // namespace
+
+extern "C" {
+
+int mfcc_b200_lifter(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t ncoeff, const double *d_lift,
+                     void *stream)
+{
+    if (n_rows < 0 || ncoeff < 1) return fail_ext(MFCC_B200_EINVAL, "bad size");
+    if (n_rows == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out || !d_lift) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_lifter<<<grid_for(n_rows * ncoeff, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n_rows * ncoeff, ncoeff, d_lift);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_standardize(const void *d_in, int32_t in_is_float, int16_t *d_out, int64_t n_frames, int32_t ncoeff,
+                          int32_t n_clips, void *stream)
+{
+    if (n_frames < 0 || ncoeff < 1 || n_clips < 0) return fail_ext(MFCC_B200_EINVAL, "bad size");
+    if (n_frames == 0 || n_clips == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    if (n_clips > 65535) return fail_ext(MFCC_B200_EINVAL, "more than 65535 clips per call");
+    const dim3 grid((unsigned)ncoeff, (unsigned)n_clips);
+    const long long pitch = n_frames * ncoeff;
+    if (in_is_float) k_standardize<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float *)d_in, d_out, n_frames, ncoeff, pitch);
+    else             k_standardize<int16_t><<<grid, 256, 0, (cudaStream_t)stream>>>((const int16_t *)d_in, d_out, n_frames, ncoeff, pitch);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_uart_frame(const int16_t *d_cols, uint8_t *d_bytes, int64_t n_cols, int32_t ncoeff, uint32_t magic,
+                         void *stream)
+{
+    if (n_cols < 0 || ncoeff < 1) return fail_ext(MFCC_B200_EINVAL, "bad size");
+    if (n_cols == 0) return MFCC_B200_OK;
+    if (!d_cols || !d_bytes) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_uart_frame<<<grid_for(n_cols * (ncoeff + 1), 256), 256, 0, (cudaStream_t)stream>>>(d_cols, d_bytes, n_cols, ncoeff, magic & 0xffffu);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_vad_step(int16_t *d_ring, int32_t *d_head, const int16_t *d_cols, int32_t n_streams, int32_t ncoeff,
+                       int32_t window, int32_t threshold, int32_t *d_power, uint8_t *d_active, void *stream)
+{
+    if (n_streams < 0 || ncoeff < 1 || window < 3) return fail_ext(MFCC_B200_EINVAL, "bad size");
+    if (n_streams == 0) return MFCC_B200_OK;
+    if (!d_ring || !d_head || !d_cols || !d_power || !d_active) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    // elements i in [size/3, 2*size/3) step ncoeff of the column-major ring (cepstrum.c:166-178)
+    const long long size = (long long)window * ncoeff;
+    const long long lo = size / 3, hi = 2 * size / 3;
+    if (lo % ncoeff) return fail_ext(MFCC_B200_EUNSUPPORTED, "window*ncoeff/3 must be a multiple of ncoeff (the host then sums c0)");
+    const int first_col = (int)(lo / ncoeff);
+    const int last_col = (int)((hi - lo + ncoeff - 1) / ncoeff) + first_col;
+    k_vad_step<<<(n_streams + 127) / 128, 128, 0, (cudaStream_t)stream>>>(d_ring, d_head, d_cols, n_streams, ncoeff, window,
+                                                                        first_col, last_col, threshold, d_power, d_active);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,85 @@
+"""Row f1: the wav2mfcc directory converter (mfcc_b200/convert.py) against the
+reference host tool's protocol restated in oracle/ref_host.py."""
+import os
+import wave
+
+import numpy as np
+import pytest
+
+from mfcc_b200 import convert
+from mfcc_b200.config import MFCCConfig
+from oracle import ref_host as H
+
+
+def write_wav(path, x, rate=16000, width=2, channels=1):
+    with wave.open(path, "wb") as w:
+        w.setnchannels(channels)
+        w.setsampwidth(width)
+        w.setframerate(rate)
+        w.writeframes(np.asarray(x).astype("<i2" if width == 2 else "u1").tobytes())
+
+
+@pytest.mark.parametrize("n", [0, 1, 100, 511, 512, 513, 681, 682, 683, 852, 5000])
+def test_host_round_count(n):
+    stream, rounds = H.host_rounds(np.arange(n) % 1000)
+    assert rounds == MFCCConfig().num_frames_host(n)
+    assert len(stream) == 512 + 170 * (rounds - 1)
+    assert np.array_equal(stream[:n], (np.arange(n) % 1000).astype(np.int16)) and not stream[n:].any()
+
+
+def test_read_wav_checks(tmp_path):
+    x = (np.arange(2000) * 7 % 3000 - 1500).astype(np.int16)
+    p = str(tmp_path / "ok.wav")
+    write_wav(p, x)
+    assert np.array_equal(convert.read_wav(p), x)
+    write_wav(str(tmp_path / "rate.wav"), x, rate=8000)
+    with pytest.raises(ValueError, match="Unexpected samplerate: 8000"):
+        convert.read_wav(str(tmp_path / "rate.wav"))
+    write_wav(str(tmp_path / "w8.wav"), np.abs(x) % 255, width=1)
+    with pytest.raises(ValueError, match="Unexpected samplesize: 1"):
+        convert.read_wav(str(tmp_path / "w8.wav"))
+    write_wav(str(tmp_path / "st.wav"), x, channels=2)
+    with pytest.raises(ValueError, match="channel"):
+        convert.read_wav(str(tmp_path / "st.wav"))
+    (tmp_path / "junk.wav").write_bytes(b"not a wav file at all")
+    with pytest.raises(ValueError, match="Unexpected format"):
+        convert.read_wav(str(tmp_path / "junk.wav"))
+
+
+def test_find_and_plan(tmp_path):
+    (tmp_path / "a" / "b").mkdir(parents=True)
+    for name in ("z.wav", "a/x.wav", "a/b/y.wav", "a/skip.txt", "a/wav"):
+        (tmp_path / name).write_bytes(b"")
+    got = [os.path.relpath(p, tmp_path) for p in convert.find_wavs(str(tmp_path))]
+    assert got == ["a/b/y.wav", "a/x.wav", "z.wav"]
+    assert convert.mfcc_path("/d/clip.wav") == "/d/clip.mfcc"
+    lengths = [16000, 100, 48000, 16000, 0, 32000]
+    b = convert.plan_batches(lengths, batch_bytes=2 * 2 * 16000)
+    assert sorted(i for g in b for i in g) == list(range(6))
+    for g in b:
+        assert len(g) * max(max(lengths[i] for i in g), 8) * 2 <= 2 * 2 * 16000 or len(g) == 1
+
+
+@pytest.mark.gpu
+def test_convert_dir_matches_host_protocol(tmp_path, wav):
+    import mfcc_b200
+    from oracle import ref_c as RC
+    cfg = RC.RefConfig(nfilters=32, nceptrums=32)
+    rng = np.random.default_rng(11)
+    clips = {"s/one.wav": wav[:16000], "s/two.wav": wav[40000:40000 + 512 + 170 * 9],
+             "t/u/short.wav": wav[:300], "t/exact.wav": wav[1000:1000 + 512],
+             "t/noise.wav": rng.integers(-32768, 32768, 7777).astype(np.int16),
+             "empty.wav": np.zeros(0, dtype=np.int16), "long.wav": wav[:70001]}
+    for rel, x in clips.items():
+        os.makedirs(os.path.dirname(str(tmp_path / rel)), exist_ok=True)
+        write_wav(str(tmp_path / rel), x)
+    write_wav(str(tmp_path / "t" / "bad_rate.wav"), wav[:1000], rate=44100)
+    op = mfcc_b200.MFCC(nfilters=32, nceptrums=32, device="cuda:0")
+    done, rejected = convert.convert_dir(str(tmp_path), op=op, batch_bytes=100000)
+    assert len(done) == len(clips) and len(rejected) == 1 and "44100" in rejected[0][1]
+    for rel, x in clips.items():
+        want = H.wav2mfcc(x, lambda s, k: RC.run(cfg, s, n_frames=k))
+        got = np.fromfile(str(tmp_path / rel)[:-3] + "mfcc", dtype=np.int16).reshape(-1, 32)
+        assert got.shape == want.shape == (MFCCConfig().num_frames_host(len(x)), 32)
+        assert np.array_equal(got, want), rel
+    assert not os.path.exists(str(tmp_path / "t" / "bad_rate.mfcc"))
