@@ -358,6 +358,22 @@ def main():
                     "h2d_bytes_per_step": ne * N_SAMPLES * 2, "d2h_bytes_per_step": ne * K * NCEP * 2},
             "gpu_launches": int(launches), "clocks": clocks,
         }
+        # instruction-issue view of the same kernel: warp-instructions per frame and DRAM bytes
+        # per frame are constants of the build, measured once with ncu (profiles/collect.py);
+        # the peak is the mixed IMAD/ALU issue rate profiles/micro/pipe_bench.cu measured
+        try:
+            iss = json.load(open(os.path.join(ROOT, "profiles", "r01_issue.json")))
+            k = iss["mfcc_int_fused"]
+            lane_rate = k["warp_inst_per_frame"] * 32 * frames_rank / t_kernel_avg
+            pk = iss["pipe_bench"]["mixed_lane_inst_per_s"]
+            line["roofline"]["traffic"] = k["dram_bytes_per_frame"] * frames_rank
+            line["roofline"]["traffic_note"] = ("%.1f B/frame from one ncu --set full capture of a 300-clip "
+                                                "launch, scaled to this launch's frames" % k["dram_bytes_per_frame"])
+            line["roofline"]["issue"] = {"achieved": lane_rate, "peak": pk, "unit": "lane-instr/s",
+                                         "frac": lane_rate / pk, "warp_inst_per_frame": k["warp_inst_per_frame"],
+                                         "peak_source": "profiles/micro/pipe_bench.cu IMAD+SHF 1:1 on this GPU model"}
+        except Exception:
+            pass
         if extras:
             extras["fp32"]["hbm_frac"] = extras["fp32"]["achieved_gbs"] / peak
             line.update(extras)

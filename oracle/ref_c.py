@@ -87,7 +87,14 @@ class RefConfig:
 
 
 def max_threads() -> int:
-    return int(lib().mfcc_ref_max_threads())
+    """Host threads the timed runs use: the cores this process may run on.  Not
+    omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1 to every rank, which would
+    silently turn the all-cores CPU baseline into a single-thread one."""
+    import os
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or int(lib().mfcc_ref_max_threads()))
 
 
 def run(cfg: RefConfig, x: np.ndarray, n_frames=None, taps=False, threads=1):
