@@ -8,8 +8,9 @@ python bench.py --impl reference > $o/${tag}_bench_reference.json 2> $o/${tag}_b
 python bench.py > $o/${tag}_bench_full.json 2> $o/${tag}_bench_full.err || tail -5 $o/${tag}_bench_full.err
 tail -c 600 $o/${tag}_bench_full.json
 profiles/micro/pipe_bench > $o/${tag}_pipe_bench.jsonl
-# launch list of the bench command (cold-cache, serialised: shares, not absolutes)
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches.csv \
+# launch list of the bench command, this library's kernels only (the synthetic-data generation is
+# thousands of torch launches); cold-cache, serialised: shares, not absolutes
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:mfcc -c 400 --csv --log-file $o/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --e2e-clips 256 --no-cpu-baseline --stream-steps 20 > /dev/null 2> $o/${tag}_launches.err
 # one full capture per fused kernel (300 clips = 1 693 500 frames per launch)
 ncu --set full --import-source on --clock-control none -k regex:mfcc_int_fused -s 2 -c 1 -f -o $o/${tag}_int python profiles/run_both.py 300 > /dev/null 2>&1
