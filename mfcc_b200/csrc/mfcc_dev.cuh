@@ -30,8 +30,12 @@ struct alignas(16) DevTables {
     int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
     int2     dct_twf[32];    // final DCT stage, lane j = bin j, doubled
     uint16_t curve[512];     // window multipliers (9 bits, unsigned), window.py:59-115
-    int16_t  seg_walk[40];   // first bin of lane's walk: segment lane+1 (lane 0: segments 0 and 1)
+    int16_t  seg_walk[40];   // word address (padded power layout) where lane's walk starts:
+                             // segment lane+1, lane 0: segments 0 and 1
     int16_t  seg_close[40];  // closing bin of mel segment g
+    uint16_t paddr[256];     // word address of bin b in the padded power layout: every segment
+                             // starts in a bank no other segment start uses, so the 32 lanes of
+                             // mel_warp() read 32 different banks at every step
     int32_t  mel_lo_bit;     // filterbank.py:122
     int32_t  nseg;
     int32_t  pad[2];
@@ -238,8 +242,8 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
 }
 
 // ---------------------------------------------------------------------------------
-// FilterBank.  pw[0..255] in shared memory (the buffer behind it is readable up to
-// pw[255 + MAXSEG]).  Returns the 16-bit mel value of filter (lane mod NF).
+// FilterBank.  pw[]: the power spectrum in shared memory in the padded layout
+// DevTables::paddr (readable MAXSEG words past its end).  Returns the 16-bit mel value of filter (lane mod NF).
 // Segment g = bins seg_first[g] .. seg_close[g].  With A_g = sum d*w over its non-closing
 // bins, D_g = sum d over them and PK_g = d at the closing bin, the register the hardware
 // reads at the close of segment g is (filterbank.py:119-142)

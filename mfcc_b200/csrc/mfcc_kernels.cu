@@ -130,7 +130,7 @@ __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, c
     for (int i = 0; i < 8; ++i) {
         const int b = lane + 32 * i;
         const unsigned pw = ((unsigned)(re[i] * re[i]) + (unsigned)(im[i] * im[i])) >> 2;
-        xbuf[b] = pw;
+        xbuf[tab->paddr[b]] = pw;
         if (TAPS && tp.d_fft) { tp.d_fft[(k * NBINS + b) * 2] = (int16_t)re[i]; tp.d_fft[(k * NBINS + b) * 2 + 1] = (int16_t)im[i]; }
         if (TAPS && tp.d_power) tp.d_power[k * NBINS + b] = pw;
     }
@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(THREADS) k_warp_stage(const void *in, void *ou
         } else if (STAGE == MFCC_B200_STAGE_MEL) {
             const uint32_t *pw = reinterpret_cast<const uint32_t *>(in) + k * NBINS;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) xbuf[lane + 32 * i] = pw[lane + 32 * i];
+            for (int i = 0; i < 8; ++i) xbuf[sm->tab.paddr[lane + 32 * i]] = pw[lane + 32 * i];
             __syncwarp();
             const unsigned mel = mel_warp<NF>(xbuf, &sm->tab, lane);
             __syncwarp();
@@ -563,7 +563,8 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
             return fail(MFCC_B200_EUNSUPPORTED, "window_curve out of the 9-bit range");
         t.curve[n] = (uint16_t)c.window_curve[n];
     }
-    int g = 0, first = 0, seg0_len = 0;
+    int g = 0, first = 0, seg0_len = 0, pad_next = 0;
+    bool bank_used[32] = {false};
     const int maxseg = (c.nfilters == 32) ? 21 : 42;
     for (int b = 0; b < NBINS; ++b) {
         if (c.mel_weight[b] >> 30) return fail(MFCC_B200_EUNSUPPORTED, "mel_weight wider than 30 bits");
@@ -576,7 +577,18 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
             const int lane_of = g == 0 ? 0 : g - 1;
             const int j0 = g == 1 ? seg0_len : 0;
             if (g == 0) seg0_len = len;
-            else t.seg_walk[g - 1] = (int16_t)(g == 1 ? 0 : first);
+            // padded power layout: segment g starts at the first free address whose bank no
+            // earlier segment start took (segment 1 follows segment 0 directly: one walk)
+            int base = pad_next;
+            if (g != 1) {
+                const int nl = c.nfilters == 32 ? 32 : 16;
+                while (bank_used[base % nl]) ++base;
+                bank_used[base % nl] = true;
+            }
+            pad_next = base + len;
+            for (int j = 0; j < len; ++j) t.paddr[first + j] = (uint16_t)(base + j);
+            if (g == 0) t.seg_walk[0] = (int16_t)base;
+            else if (g > 1) t.seg_walk[g - 1] = (int16_t)base;
             if (j0 + len > maxseg || g > c.nfilters) return fail(MFCC_B200_EUNSUPPORTED, "mel segment too long for the kernel's table");
             for (int j = 0; j < len; ++j) {
                 const bool closing = (first + j == b);
@@ -590,6 +602,7 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
     }
     if (g != c.nfilters + 1 || first != NBINS)
         return fail(MFCC_B200_EUNSUPPORTED, "mel tables must describe nfilters+1 segments ending at the last bin");
+    if (pad_next + maxseg > XW) return fail(MFCC_B200_EUNSUPPORTED, "padded power layout does not fit the exchange buffer");
     for (int z = 0; z < 2048; ++z) t.logfrac[z] = (uint16_t)log2fix_frac(2048u + z);
     t.nseg = g;
     t.mel_lo_bit = c.mel_lo_bit;

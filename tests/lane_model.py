@@ -175,6 +175,31 @@ def mel_tables(nfilters, samplerate=16e3, nfft=512):
     return ab, bounds
 
 
+def mel_padded_layout(nfilters, samplerate=16e3, nfft=512):
+    """DevTables::paddr / seg_walk as mfcc_b200_create() builds them: segment g starts at
+    the first free word whose bank no earlier segment start took (segment 1 follows
+    segment 0 directly: lane 0 walks both)."""
+    bounds = T.mel_segment_bounds(nfilters, nfft, samplerate)
+    nl = 32 if nfilters == 32 else 16
+    used, nxt = set(), 0
+    paddr = np.zeros(nfft // 2, dtype=np.int64)
+    walk = np.zeros(nfilters, dtype=np.int64)
+    for g, (first, cl) in enumerate(bounds):
+        base = nxt
+        if g != 1:
+            while base % nl in used:
+                base += 1
+            used.add(base % nl)
+        n = cl - first + 1
+        paddr[first:first + n] = base + np.arange(n)
+        nxt = base + n
+        if g == 0:
+            walk[0] = base
+        elif g > 1:
+            walk[g - 1] = base
+    return paddr, walk, nxt
+
+
 def mel_lanes(pw, nfilters, samplerate=16e3, nfft=512, lo_bit=31):
     """Lane g-1 walks segment g (lane 0: segments 0 and 1) with two 64-bit multiply-adds
     per step (fixed trip count, zero-padded weights); filter g-1 = Abar_{g-1} (from the
@@ -182,11 +207,13 @@ def mel_lanes(pw, nfilters, samplerate=16e3, nfft=512, lo_bit=31):
     ab, bounds = mel_tables(nfilters, samplerate, nfft)
     maxseg = ab.shape[0]
     M64 = (1 << 64) - 1
-    pwx = np.concatenate([np.asarray(pw, dtype=np.int64), np.full(maxseg + 8, 12345)])   # readable overrun
+    paddr, walk, end = mel_padded_layout(nfilters, samplerate, nfft)
+    pwx = np.full(end + maxseg + 8, 12345, dtype=np.int64)      # gaps and overrun hold garbage
+    pwx[paddr] = np.asarray(pw, dtype=np.int64)
     a = [0] * nfilters
     b = [0] * nfilters
     for li in range(nfilters):
-        first = 0 if li == 0 else bounds[li + 1][0]
+        first = int(walk[li])
         for j in range(maxseg):
             d = int(pwx[first + j])
             a[li] = (a[li] + d * int(ab[j, li, 0])) & M64

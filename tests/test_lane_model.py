@@ -72,3 +72,16 @@ def test_log2_table_equals_the_loop():
     t = LM.log2_table()
     for m in list(range(0, 4200)) + list(range(60000, 65536)) + [32767, 32768, 16384, 9999]:
         assert LM.log2_tab_lane(m, t) == LM.log2_lane(m)
+
+
+@pytest.mark.parametrize("nf", [16, 32])
+def test_mel_padded_layout_is_conflict_free(nf):
+    paddr, walk, end = LM.mel_padded_layout(nf)
+    maxseg = 21 if nf == 32 else 42
+    assert len(set(paddr.tolist())) == 256 and end + maxseg <= 656        # injective, fits xbuf
+    lanes = nf if nf == 32 else 16
+    for j in range(maxseg if nf == 32 else maxseg // 2):
+        assert LM.bank_conflict_degree(walk[:lanes] + j) == 1
+    # the power stores (lane handles bins lane + 32 i) stay cheap
+    worst = max(LM.bank_conflict_degree(paddr[np.arange(32) + 32 * i]) for i in range(8))
+    assert worst <= 2
