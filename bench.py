@@ -325,6 +325,27 @@ def main():
                           "achieved_gbs": frames_rank * (170 * 2 + NCEP * 4) / tf / 1e9,
                           "kernel": "mfcc_f32_fused<32>", "finite": bool(torch.isfinite(outf[:64]).all())}
         del outf
+        # the librosa feature set of software/genlibrosa.py (BASELINE.json configs[2]'s comparison
+        # arm): 2048-point frames, 128 mel filters, dB floor, 32 coefficients; float32
+        opl = mfcc_b200.LibrosaMFCC(sr=16000, hop_length=170, n_mfcc=32, device=dev)
+        nl = min(args.clips, 8192)
+        xl = x[:nl]
+        Kl = opl.num_frames(xl.shape[1])
+        outl = torch.empty((nl, Kl, 32), dtype=torch.float32, device=dev)
+        for _ in range(3):
+            opl(xl, out=outl)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(fsteps):
+            opl(xl, out=outl)
+        e1.record()
+        torch.cuda.synchronize()
+        tl = e0.elapsed_time(e1) * 1e-3 / fsteps
+        extras["librosa_set"] = {"value": nl * Kl / tl, "unit": "frames/s", "ms_per_step": tl * 1e3,
+                                 "clips": nl, "frames_per_clip": Kl, "steps": fsteps,
+                                 "kernels": ["lr_logmel", "lr_dct"],
+                                 "finite": bool(torch.isfinite(outl[:64]).all())}
+        del outl, opl
         extras["streaming"] = stream_latency(op, dev, 4096, args.stream_steps)
         extras["streaming_fp32"] = stream_latency(opf, dev, 4096, max(1000, args.stream_steps // 5))
 

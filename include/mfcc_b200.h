@@ -186,6 +186,46 @@ int  mfcc_b200_vad_step(int16_t *d_ring, int32_t *d_head, const int16_t *d_cols,
                         int32_t ncoeff, int32_t window, int32_t threshold, int32_t *d_power,
                         uint8_t *d_active, void *stream);
 
+/*
+ * ---- the librosa parameter set of the comparison script ----
+ * software/genlibrosa.py:21-24 computes librosa.feature.mfcc(samples, sr=16000,
+ * hop_length=170, n_mfcc=32) for every clip; librosa's defaults fill in the rest:
+ * n_fft 2048, Hann window, centred frames over reflect padding, power spectrogram,
+ * 128 Slaney mel filters, power_to_db (ref 1, amin 1e-10, top_db 80), orthonormal
+ * DCT-II.  Tables are HOST arrays copied by create (mfcc_b200/tables.py lr_* build them).
+ * Output is float32, time-major [n_frames][n_mfcc] per clip (librosa returns the
+ * transpose).
+ */
+typedef struct mfcc_b200_librosa_cfg {
+    int32_t struct_size;     /* sizeof(mfcc_b200_librosa_cfg) */
+    int32_t n_fft;           /* 2048 (the size the kernels cover) */
+    int32_t hop;             /* 170                     software/genlibrosa.py:23 */
+    int32_t n_mels;          /* 1..128, librosa default 128 */
+    int32_t n_mfcc;          /* 1..min(64, n_mels), 32 in software/genlibrosa.py:24 */
+    int32_t center;          /* 1: frame t is centred on sample t*hop over reflect padding */
+    float   amin;            /* 1e-10 */
+    float   top_db;          /* 80; negative = no floor (librosa top_db=None) */
+    const float *window;     /* [n_fft], already divided by the int16 full scale 32768 */
+    const float *mel;        /* [n_mels][n_fft/2+1] dense filter matrix */
+    const float *dct;        /* [n_mfcc][n_mels] */
+} mfcc_b200_librosa_cfg;
+
+typedef struct mfcc_b200_librosa_taps {   /* device pointers, any may be NULL; n_clips == 1 */
+    float *d_power;          /* [K][n_fft/2+1] */
+    float *d_logmel;         /* [K][n_mels], before the top_db floor */
+} mfcc_b200_librosa_taps;
+
+int     mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle);
+void    mfcc_b200_librosa_destroy(void *handle);
+/* librosa's frame count for a clip: 1 + n_samples / hop when centred. */
+int64_t mfcc_b200_librosa_frames(void *handle, int64_t n_samples);
+/* Bytes of device scratch mfcc_b200_librosa_run needs (log-mel matrix + per-clip maxima:
+ * the dB floor depends on the maximum over the whole clip, so the path has two passes). */
+int     mfcc_b200_librosa_workspace(void *handle, int32_t n_clips, int64_t n_frames, int64_t *bytes);
+int     mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t n_samples,
+                              int32_t n_clips, int64_t n_frames, void *d_work, float *d_out,
+                              int64_t out_clip_stride, const mfcc_b200_librosa_taps *taps, void *stream);
+
 /* Number of kernels this library has launched since it was loaded (bench.py's
  * gpu_launches). */
 int64_t     mfcc_b200_launch_count(void);

@@ -14,6 +14,9 @@ def __getattr__(name):
     if name == "MFCC":
         from .mfcc import MFCC
         return MFCC
+    if name == "LibrosaMFCC":
+        from .librosa_mode import LibrosaMFCC
+        return LibrosaMFCC
     if name in ("Preemph", "Frame", "WindowHamming", "FftStream", "PowerSpectrum", "FilterBank",
                 "Log2Fix", "DCTStream", "Discard"):
         from . import stages

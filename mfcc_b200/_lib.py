@@ -33,6 +33,15 @@ class Taps(C.Structure):
                                           "d_dct")]
 
 
+class LibrosaCfg(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("struct_size", "n_fft", "hop", "n_mels", "n_mfcc", "center")] + [
+        ("amin", C.c_float), ("top_db", C.c_float)] + [(n, C.c_void_p) for n in ("window", "mel", "dct")]
+
+
+class LibrosaTaps(C.Structure):
+    _fields_ = [("d_power", C.c_void_p), ("d_logmel", C.c_void_p)]
+
+
 class MfccError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__("libmfcc_b200: %s (code %d)" % (msg, code))
@@ -75,6 +84,16 @@ def lib():
     L.mfcc_b200_uart_frame.argtypes = [vp, vp, i64, i32, C.c_uint32, vp]
     L.mfcc_b200_vad_step.restype = C.c_int
     L.mfcc_b200_vad_step.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp, vp]
+    L.mfcc_b200_librosa_create.restype = C.c_int
+    L.mfcc_b200_librosa_create.argtypes = [C.POINTER(LibrosaCfg), C.POINTER(vp)]
+    L.mfcc_b200_librosa_destroy.restype = None
+    L.mfcc_b200_librosa_destroy.argtypes = [vp]
+    L.mfcc_b200_librosa_frames.restype = C.c_int64
+    L.mfcc_b200_librosa_frames.argtypes = [vp, i64]
+    L.mfcc_b200_librosa_workspace.restype = C.c_int
+    L.mfcc_b200_librosa_workspace.argtypes = [vp, i32, i64, C.POINTER(i64)]
+    L.mfcc_b200_librosa_run.restype = C.c_int
+    L.mfcc_b200_librosa_run.argtypes = [vp, vp, i64, i64, i32, i64, vp, vp, i64, C.POINTER(LibrosaTaps), vp]
     L.mfcc_b200_launch_count.restype = C.c_int64
     L.mfcc_b200_launch_count.argtypes = []
     L.mfcc_b200_last_error.restype = C.c_char_p
@@ -88,6 +107,8 @@ def lib():
 EXPORTS = ["mfcc_b200_create", "mfcc_b200_destroy", "mfcc_b200_run", "mfcc_b200_run_host",
            "mfcc_b200_stage", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_lifter",
            "mfcc_b200_standardize", "mfcc_b200_uart_frame", "mfcc_b200_vad_step",
+           "mfcc_b200_librosa_create", "mfcc_b200_librosa_destroy", "mfcc_b200_librosa_frames",
+           "mfcc_b200_librosa_workspace", "mfcc_b200_librosa_run",
            "mfcc_b200_launch_count", "mfcc_b200_last_error", "mfcc_b200_version"]
 
 

@@ -7,8 +7,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SRC = os.path.join(_HERE, "csrc")
-SOURCES = ["mfcc_kernels.cu", "mfcc_post.cu"]
-DEPS = ["mfcc_kernels.cu", "mfcc_post.cu", "mfcc_dev.cuh", "mfcc_f32.cuh", os.path.join("..", "..", "include", "mfcc_b200.h")]
+SOURCES = ["mfcc_kernels.cu", "mfcc_post.cu", "mfcc_librosa.cu"]
+DEPS = ["mfcc_kernels.cu", "mfcc_post.cu", "mfcc_librosa.cu", "mfcc_dev.cuh", "mfcc_f32.cuh", os.path.join("..", "..", "include", "mfcc_b200.h")]
 OUT = os.path.join(_HERE, "libmfcc_b200.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -206,3 +206,53 @@ def f_dct_matrix(n: int = 32) -> np.ndarray:
     d = np.cos(np.pi * (m + 0.5) * k / n) * np.sqrt(2.0 / n)
     d[0] *= np.sqrt(0.5)
     return d
+
+
+# ----------------------------------------------------------------------------- librosa set
+# Tables of librosa.feature.mfcc with the arguments of software/genlibrosa.py:21-24 and
+# librosa's defaults for the rest (librosa is not part of /root/reference; these restate
+# its published definitions).  Built in float64, handed to the library as float32.
+
+def lr_hz_to_mel(f):
+    """Slaney mel scale: linear (200/3 Hz per mel) below 1 kHz, logarithmic above with
+    27 mels per factor 6.4."""
+    f = np.asarray(f, dtype=np.float64)
+    lin = f * (3.0 / 200.0)
+    with np.errstate(divide="ignore"):
+        log = 15.0 + np.log(f / 1000.0) * (27.0 / np.log(6.4))
+    return np.where(f >= 1000.0, log, lin)
+
+
+def lr_mel_to_hz(m):
+    m = np.asarray(m, dtype=np.float64)
+    return np.where(m >= 15.0, 1000.0 * np.exp((m - 15.0) * (np.log(6.4) / 27.0)), m * (200.0 / 3.0))
+
+
+def lr_mel_filters(samplerate: float = 16000, n_fft: int = 2048, n_mels: int = 128,
+                   fmin: float = 0.0, fmax=None) -> np.ndarray:
+    """Dense [n_mels][n_fft/2+1] triangular filters on Slaney-spaced centres, each scaled
+    to constant area (2 / bandwidth)."""
+    fmax = samplerate / 2.0 if fmax is None else float(fmax)
+    bins = np.arange(n_fft // 2 + 1) * (samplerate / n_fft)
+    edges = lr_mel_to_hz(np.linspace(lr_hz_to_mel(fmin), lr_hz_to_mel(fmax), n_mels + 2))
+    out = np.zeros((n_mels, bins.size))
+    for i in range(n_mels):
+        lo, mid, hi = edges[i], edges[i + 1], edges[i + 2]
+        rise = (bins - lo) / (mid - lo)
+        fall = (hi - bins) / (hi - mid)
+        out[i] = np.clip(np.minimum(rise, fall), 0.0, None) * (2.0 / (hi - lo))
+    return out
+
+
+def lr_window(n_fft: int = 2048) -> np.ndarray:
+    """Periodic Hann, 0.5 - 0.5 cos(2 pi n / n_fft)."""
+    return 0.5 - 0.5 * np.cos(2.0 * np.pi * np.arange(n_fft) / n_fft)
+
+
+def lr_dct_matrix(n_mfcc: int = 32, n_mels: int = 128) -> np.ndarray:
+    """First n_mfcc rows of the orthonormal DCT-II of length n_mels."""
+    k = np.arange(n_mfcc)[:, None]
+    m = np.arange(n_mels)[None, :]
+    d = np.cos(np.pi * (m + 0.5) * k / n_mels) * np.sqrt(2.0 / n_mels)
+    d[0] *= np.sqrt(0.5)
+    return d
