@@ -403,8 +403,10 @@ def main():
             thr = RC.max_threads()
             ncl = min(256, 16 * thr)        # ~20 core-seconds of CPU work
             v, fr, dt = cpu_oracle_rate(ncl, thr)
+            v1, fr1, dt1 = cpu_oracle_rate(16, 1)       # also a single-thread figure
             line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": thr, "kind": "port",
-                                    "sample": "%d clips x 60 s (%d frames), %.1f s" % (ncl, fr, dt)}
+                                    "sample": "%d clips x 60 s (%d frames), %.1f s" % (ncl, fr, dt),
+                                    "single_thread": {"value": v1, "sample": "16 clips x 60 s, %.1f s" % dt1}}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -53,10 +53,13 @@ class LibrosaMFCC:
         self._work = None
 
     def __del__(self):
-        h = getattr(self, "_h", None)
-        if h:
-            _lib.lib().mfcc_b200_librosa_destroy(h)
-            self._h = None
+        try:
+            h = getattr(self, "_h", None)
+            if h:
+                _lib.lib().mfcc_b200_librosa_destroy(h)
+                self._h = None
+        except Exception:       # interpreter shutdown: module globals may be gone
+            pass
 
     def num_frames(self, n_samples: int) -> int:
         """librosa's frame count: ``1 + n // hop_length`` for centred frames."""

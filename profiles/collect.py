@@ -27,16 +27,19 @@ def to_bytes(v, u):
 
 
 def main():
+    global FRAMES
     tag = sys.argv[1]
-    for suffix in ("bench_full.json", "bench_reference.json", "launches.csv", "pipe_bench.jsonl", "pytest.txt"):
+    for suffix in ("bench_full.json", "bench_reference.json", "launches.csv", "pipe_bench.jsonl", "pytest.txt",
+                   "librosa_rate.txt"):
         src = os.path.join(G, "%s_%s" % (tag, suffix))
         if os.path.exists(src):
             shutil.copy(src, os.path.join(P, "%s_%s" % (tag, suffix)))
     issue = {"source": "profiles/final.sh %s" % tag, "frames_per_profiled_launch": FRAMES}
-    for k, name in (("int", "mfcc_int_fused"), ("f32", "mfcc_f32_fused")):
+    for k, name in (("int", "mfcc_int_fused"), ("f32", "mfcc_f32_fused"), ("lr", "lr_logmel")):
         rep = os.path.join(G, "%s_%s.ncu-rep" % (tag, k))
         if not os.path.exists(rep):
             continue
+        FRAMES = 300 * (5648 if k == "lr" else 5645)
         with open(os.path.join(P, "%s_%s_ncu_full.txt" % (tag, k)), "w") as f:
             f.write(subprocess.run([sys.executable, os.path.join(P, "summarize_ncu.py"), rep, str(FRAMES)],
                                    capture_output=True, text=True).stdout)

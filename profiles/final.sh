@@ -10,9 +10,11 @@ tail -c 600 $o/${tag}_bench_full.json
 profiles/micro/pipe_bench > $o/${tag}_pipe_bench.jsonl
 # launch list of the bench command, this library's kernels only (the synthetic-data generation is
 # thousands of torch launches); cold-cache, serialised: shares, not absolutes
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:mfcc -c 400 --csv --log-file $o/${tag}_launches.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:mfcc|lr_" -c 400 --csv --log-file $o/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --e2e-clips 256 --no-cpu-baseline --stream-steps 20 > /dev/null 2> $o/${tag}_launches.err
 # one full capture per fused kernel (300 clips = 1 693 500 frames per launch)
 ncu --set full --import-source on --clock-control none -k regex:mfcc_int_fused -s 2 -c 1 -f -o $o/${tag}_int python profiles/run_both.py 300 > /dev/null 2>&1
 ncu --set full --import-source on --clock-control none -k regex:mfcc_f32_fused -s 2 -c 1 -f -o $o/${tag}_f32 python profiles/run_both.py 300 > /dev/null 2>&1
+ncu --set full --import-source on --clock-control none -k regex:lr_logmel -s 3 -c 1 -f -o $o/${tag}_lr python profiles/run_librosa.py 300 > /dev/null 2>&1
+python profiles/run_librosa.py 300 > $o/${tag}_librosa_rate.txt 2>/dev/null
 ls -la $o | tail -12
