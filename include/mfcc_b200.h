@@ -166,6 +166,9 @@ int  mfcc_b200_lifter(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32
 int  mfcc_b200_standardize(const void *d_in, int32_t in_is_float, int16_t *d_out, int64_t n_frames,
                            int32_t ncoeff, int32_t n_clips, void *stream);
 
+/* spec.astype(np.int16) of float32 features (software/genlibrosa.py:27): truncation toward zero. */
+int  mfcc_b200_to_int16(const float *d_in, int16_t *d_out, int64_t n, void *stream);
+
 /*
  * Serial framing of cepstrum columns, MagicInserter (mfcc/misc/magic.py:27-39) and the
  * byte order of the UART sender (mfcc/targets/mic2mfcc.py:58-62); what

@@ -125,16 +125,86 @@ def convert_dir(root: str, op=None, nfilters: int = 32, nceptrums: int = 32,
     return sorted(done), rejected
 
 
+def read_wav_any_rate(path: str):
+    """(samples int16, rate): ``librosa.load(wav, sr=None)`` keeps the file's rate
+    (software/genlibrosa.py:21); mono 16-bit PCM only, like the rest of the tool chain."""
+    try:
+        w = wave.open(path, "rb")
+    except (wave.Error, EOFError) as e:
+        raise ValueError("Unexpected format: %s (%s)" % (e, path)) from None
+    with w:
+        if w.getsampwidth() != 2 or w.getnchannels() != 1:
+            raise ValueError("Unexpected format: %d bytes/sample, %d channels (%s)"
+                             % (w.getsampwidth(), w.getnchannels(), path))
+        rate = w.getframerate()
+        data = w.readframes(w.getnframes())
+    return np.frombuffer(data, dtype="<i2").astype(np.int16, copy=False), rate
+
+
+def convert_dir_librosa(root: str, ncepstrums: int = 32, hop_length: int = 170, device=None,
+                        batch_bytes: int = 256 << 20, verbose: bool = False):
+    """The loop of software/genlibrosa.py:15-28 on the GPU: for every ``root/*/*.wav``
+    write ``<name>.spec`` (``librosa.feature.mfcc(..., hop_length=170, n_mfcc=32)`` cast to
+    int16) and ``<name>.sklearn`` (the same features standardised over time, cast to
+    int16), both laid out ``[n_mfcc][frames]`` as the script's ``tofile`` leaves them.
+
+    Clips of equal length and rate share a launch (the reflect padding at the end of a
+    clip depends on its length, so rows of one launch must be equally long)."""
+    import glob
+    import torch
+    from . import post
+    from .librosa_mode import LibrosaMFCC
+    names = sorted(glob.glob(os.path.join(root, "*", "*.wav")))          # genlibrosa.py:15
+    groups, rejected = {}, []
+    for p in names:
+        try:
+            x, rate = read_wav_any_rate(p)
+            if len(x) < 1:
+                raise ValueError("empty file (%s)" % p)
+            groups.setdefault((rate, len(x)), []).append((p, x))
+        except ValueError as e:
+            rejected.append((p, str(e)))
+            if verbose:
+                print(e)
+    done, ops = [], {}
+    for (rate, n), items in sorted(groups.items()):
+        op = ops.get(rate)
+        if op is None:
+            op = ops[rate] = LibrosaMFCC(sr=rate, n_mfcc=ncepstrums, hop_length=hop_length, device=device)
+        per = max(1, batch_bytes // max(2 * n, 1))
+        for i in range(0, len(items), per):
+            part = items[i:i + per]
+            xh = torch.from_numpy(np.stack([x for _p, x in part])).pin_memory()
+            feat = op(xh.to(op.device, non_blocking=True))               # [B, K, n_mfcc] float32
+            spec = post.to_int16(feat).cpu().numpy()
+            skl = post.scale(feat).cpu().numpy()
+            for j, (p, _x) in enumerate(part):
+                base = os.path.splitext(p)[0]
+                np.ascontiguousarray(spec[j].T).tofile(base + ".spec")       # genlibrosa.py:27
+                np.ascontiguousarray(skl[j].T).tofile(base + ".sklearn")     # genlibrosa.py:28
+                done.append((p, base + ".spec", base + ".sklearn", spec.shape[1]))
+                if verbose:
+                    print(p, base + ".spec")
+    return sorted(done), rejected
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description="wav2mfcc on the GPU: *.wav -> *.mfcc")
     ap.add_argument("wavdir")
     ap.add_argument("--nfilters", type=int, default=32)
     ap.add_argument("--nceptrums", type=int, default=32)
     ap.add_argument("--batch-mb", type=int, default=256)
+    ap.add_argument("--librosa", action="store_true",
+                    help="write .spec/.sklearn like software/genlibrosa.py instead of .mfcc")
     a = ap.parse_args(argv)
     if not os.path.isdir(a.wavdir):
         print("Usage: %s <wavdir>" % sys.argv[0])            # software/main.c:250-253
         return 1
+    if a.librosa:
+        done, rejected = convert_dir_librosa(a.wavdir, ncepstrums=a.nceptrums, batch_bytes=a.batch_mb << 20,
+                                             verbose=True)
+        print("%d files converted, %d rejected" % (len(done), len(rejected)))
+        return 0
     done, rejected = convert_dir(a.wavdir, nfilters=a.nfilters, nceptrums=a.nceptrums,
                                  batch_bytes=a.batch_mb << 20, verbose=True)
     print("%d files converted, %d rejected" % (len(done), len(rejected)))

@@ -109,6 +109,12 @@ __global__ void k_vad_step(int16_t *ring, int *head, const int16_t *cols, int n_
     active[s] = (int)p >= threshold;
 }
 
+// ndarray.astype(np.int16) of a float32 array (software/genlibrosa.py:27)
+__global__ void k_to_int16(const float *in, int16_t *out, long long total) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+        out[i] = trunc16((double)in[i]);
+}
+
 inline int grid_for(long long total, int block) {
     long long g = (total + block - 1) / block;
     if (g > 148 * 16) g = 148 * 16;
@@ -133,6 +139,16 @@ int mfcc_b200_lifter(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_
     if (n_rows == 0) return MFCC_B200_OK;
     if (!d_in || !d_out || !d_lift) return fail_ext(MFCC_B200_EINVAL, "null buffer");
     k_lifter<<<grid_for(n_rows * ncoeff, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n_rows * ncoeff, ncoeff, d_lift);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_to_int16(const float *d_in, int16_t *d_out, int64_t n, void *stream)
+{
+    if (n < 0) return fail_ext(MFCC_B200_EINVAL, "bad size");
+    if (n == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_to_int16<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
 }

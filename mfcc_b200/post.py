@@ -75,6 +75,17 @@ def scale(cepstra):
     return out
 
 
+def to_int16(x):
+    """float32 CUDA tensor -> int16 like ``ndarray.astype(np.int16)`` (software/genlibrosa.py:27)."""
+    if not isinstance(x, torch.Tensor) or x.dtype != torch.float32 or x.device.type != "cuda":
+        raise TypeError("x must be a CUDA float32 tensor")
+    x = x.contiguous()
+    out = torch.empty(x.shape, dtype=torch.int16, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().mfcc_b200_to_int16(_p(x), _p(out), x.numel(), _sp(x)))
+    return out
+
+
 def uart_frame(cols, magic=MAGIC):
     """int16 ``[n, ncoeff]`` -> uint8 ``[n, 2 * (ncoeff + 1)]``: the bytes the microphone
     build puts on the serial line for these columns."""

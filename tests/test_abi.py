@@ -17,7 +17,7 @@ def libpath():
 
 def test_header_symbols_exported(libpath):
     hdr = open(os.path.join(ROOT, "include", "mfcc_b200.h")).read()
-    declared = set(re.findall(r"\b(mfcc_b200_[a-z_]+)\s*\(", hdr))
+    declared = set(re.findall(r"\b(mfcc_b200_[a-z0-9_]+)\s*\(", hdr))
     assert len(declared) >= 10
     lib = ctypes.CDLL(libpath)
     for name in declared:

@@ -83,3 +83,32 @@ def test_convert_dir_matches_host_protocol(tmp_path, wav):
         assert got.shape == want.shape == (MFCCConfig().num_frames_host(len(x)), 32)
         assert np.array_equal(got, want), rel
     assert not os.path.exists(str(tmp_path / "t" / "bad_rate.mfcc"))
+
+
+@pytest.mark.gpu
+def test_convert_dir_librosa_writes_spec_and_sklearn(tmp_path, wav):
+    """software/genlibrosa.py:15-28: <dir>/*/*.wav -> .spec and .sklearn, int16 [32][frames]."""
+    from oracle import ref_librosa as L
+    rng = np.random.default_rng(12)
+    clips = {"a/one.wav": wav[:16000], "a/two.wav": wav[50000:66000], "b/three.wav": wav[90000:95000],
+             "b/noise.wav": np.clip(rng.normal(0, 3000, 16000), -32768, 32767).astype(np.int16)}
+    for rel, x in clips.items():
+        os.makedirs(os.path.dirname(str(tmp_path / rel)), exist_ok=True)
+        write_wav(str(tmp_path / rel), x)
+    write_wav(str(tmp_path / "top_level_is_not_globbed.wav"), wav[:1000])
+    write_wav(str(tmp_path / "b" / "stereo.wav"), wav[:1000], channels=2)
+    done, rejected = convert.convert_dir_librosa(str(tmp_path), device="cuda:0")
+    assert len(done) == len(clips) and len(rejected) == 1
+    for rel, x in clips.items():
+        base = str(tmp_path / rel)[:-4]
+        K = 1 + len(x) // 170                                   # 95 for one second: NFRAMES of software/view.py:37
+        spec = np.fromfile(base + ".spec", dtype=np.int16).reshape(32, K)
+        skl = np.fromfile(base + ".sklearn", dtype=np.int16).reshape(32, K)
+        ref = L.mfcc(x)                                          # [K][32] float64
+        for got, want in ((spec, ref.T), (skl, H.scale_time(ref).T)):
+            tr = np.trunc(want)
+            near = np.abs(want - np.round(want)) < 1e-2          # float32 noise may cross a truncation boundary
+            assert np.array_equal(got[~near], tr[~near].astype(np.int16)), rel
+            assert np.abs(got - tr).max() <= 1
+    assert 1 + 16000 // 170 == 95
+    assert not os.path.exists(str(tmp_path / "top_level_is_not_globbed.spec"))
