@@ -305,49 +305,58 @@ def main():
 
     extras = {}
     if world == 1 and not args.no_extras:
-        # fp32 mode on the same clips (config C3's throughput leg; parity is in tests/)
+        # Extra legs of the N=1 line.  Each is guarded: a failure is recorded in the line
+        # and can never cost the headline numbers measured above.
         del xh, oh
-        opf = mfcc_b200.MFCC(nfilters=NFILT, nceptrums=NCEP, mode="fp32", mel_floor=1e-3, device=dev)
-        outf = torch.empty((args.clips, K, NCEP), dtype=torch.float32, device=dev)
-        for _ in range(3):
-            opf(x, out=outf)
-        torch.cuda.synchronize()
         fsteps = max(3, min(args.steps, 5))
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(fsteps):
-            opf(x, out=outf)
-        e1.record()
-        torch.cuda.synchronize()
-        tf = e0.elapsed_time(e1) * 1e-3 / fsteps
-        extras["fp32"] = {"value": frames_rank / tf, "unit": "frames/s", "ms_per_step": tf * 1e3,
-                          "steps": fsteps, "bytes_per_frame": 170 * 2 + NCEP * 4,
-                          "achieved_gbs": frames_rank * (170 * 2 + NCEP * 4) / tf / 1e9,
-                          "kernel": "mfcc_f32_fused<32>", "finite": bool(torch.isfinite(outf[:64]).all())}
-        del outf
-        # the librosa feature set of software/genlibrosa.py (BASELINE.json configs[2]'s comparison
-        # arm): 2048-point frames, 128 mel filters, dB floor, 32 coefficients; float32
-        opl = mfcc_b200.LibrosaMFCC(sr=16000, hop_length=170, n_mfcc=32, device=dev)
-        nl = min(args.clips, 8192)
-        xl = x[:nl]
-        Kl = opl.num_frames(xl.shape[1])
-        outl = torch.empty((nl, Kl, 32), dtype=torch.float32, device=dev)
-        for _ in range(3):
-            opl(xl, out=outl)
-        torch.cuda.synchronize()
-        e0.record()
-        for _ in range(fsteps):
-            opl(xl, out=outl)
-        e1.record()
-        torch.cuda.synchronize()
-        tl = e0.elapsed_time(e1) * 1e-3 / fsteps
-        extras["librosa_set"] = {"value": nl * Kl / tl, "unit": "frames/s", "ms_per_step": tl * 1e3,
-                                 "clips": nl, "frames_per_clip": Kl, "steps": fsteps,
-                                 "kernels": ["lr_logmel", "lr_dct"],
-                                 "finite": bool(torch.isfinite(outl[:64]).all())}
-        del outl, opl
-        extras["streaming"] = stream_latency(op, dev, 4096, args.stream_steps)
-        extras["streaming_fp32"] = stream_latency(opf, dev, 4096, max(1000, args.stream_steps // 5))
+
+        def timed(fn):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(fsteps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) * 1e-3 / fsteps
+
+        def leg_fp32():
+            # fp32 mode on the same clips (config C3's throughput leg; parity is in tests/)
+            opf = mfcc_b200.MFCC(nfilters=NFILT, nceptrums=NCEP, mode="fp32", mel_floor=1e-3, device=dev)
+            outf = torch.empty((args.clips, K, NCEP), dtype=torch.float32, device=dev)
+            tf = timed(lambda: opf(x, out=outf))
+            return {"value": frames_rank / tf, "unit": "frames/s", "ms_per_step": tf * 1e3,
+                    "steps": fsteps, "bytes_per_frame": 170 * 2 + NCEP * 4,
+                    "achieved_gbs": frames_rank * (170 * 2 + NCEP * 4) / tf / 1e9,
+                    "kernel": "mfcc_f32_fused<32>", "finite": bool(torch.isfinite(outf[:64]).all())}
+
+        def leg_librosa():
+            # the librosa feature set of software/genlibrosa.py (BASELINE.json configs[2]'s
+            # comparison arm): 2048-point frames, 128 mel filters, dB floor, 32 coefficients
+            opl = mfcc_b200.LibrosaMFCC(sr=16000, hop_length=170, n_mfcc=32, device=dev)
+            nl = min(args.clips, 4096)
+            xl = x[:nl]
+            Kl = opl.num_frames(xl.shape[1])
+            outl = torch.empty((nl, Kl, 32), dtype=torch.float32, device=dev)
+            tl = timed(lambda: opl(xl, out=outl))
+            return {"value": nl * Kl / tl, "unit": "frames/s", "ms_per_step": tl * 1e3,
+                    "clips": nl, "frames_per_clip": Kl, "steps": fsteps,
+                    "kernels": ["lr_logmel", "lr_dct"], "finite": bool(torch.isfinite(outl[:64]).all())}
+
+        def leg_stream_fp32():
+            opf = mfcc_b200.MFCC(nfilters=NFILT, nceptrums=NCEP, mode="fp32", mel_floor=1e-3, device=dev)
+            return stream_latency(opf, dev, 4096, max(1000, args.stream_steps // 5))
+
+        for name, leg in (("fp32", leg_fp32), ("librosa_set", leg_librosa),
+                          ("streaming", lambda: stream_latency(op, dev, 4096, args.stream_steps)),
+                          ("streaming_fp32", leg_stream_fp32)):
+            try:
+                extras[name] = leg()
+            except Exception as e:      # noqa: BLE001 - reported, never fatal
+                extras[name] = {"error": "%s: %s" % (type(e).__name__, e)}
+            torch.cuda.empty_cache()
 
     if rank == 0:
         peaks = {}
@@ -396,17 +405,22 @@ def main():
         except Exception:
             pass
         if extras:
-            extras["fp32"]["hbm_frac"] = extras["fp32"]["achieved_gbs"] / peak
+            if "achieved_gbs" in extras.get("fp32", {}):
+                extras["fp32"]["hbm_frac"] = extras["fp32"]["achieved_gbs"] / peak
             line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
-            from oracle import ref_c as RC
-            thr = RC.max_threads()
-            ncl = min(256, 16 * thr)        # ~20 core-seconds of CPU work
-            v, fr, dt = cpu_oracle_rate(ncl, thr)
-            v1, fr1, dt1 = cpu_oracle_rate(16, 1)       # also a single-thread figure
-            line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": thr, "kind": "port",
-                                    "sample": "%d clips x 60 s (%d frames), %.1f s" % (ncl, fr, dt),
-                                    "single_thread": {"value": v1, "sample": "16 clips x 60 s, %.1f s" % dt1}}
+            try:
+                from oracle import ref_c as RC
+                thr = RC.max_threads()
+                ncl = min(256, 16 * thr)        # ~20 core-seconds of CPU work
+                v, fr, dt = cpu_oracle_rate(ncl, thr)
+                v1, fr1, dt1 = cpu_oracle_rate(16, 1)       # also a single-thread figure
+                line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": thr, "kind": "port",
+                                        "sample": "%d clips x 60 s (%d frames), %.1f s" % (ncl, fr, dt),
+                                        "single_thread": {"value": v1, "sample": "16 clips x 60 s, %.1f s" % dt1}}
+            except Exception as e:      # noqa: BLE001
+                line["cpu_baseline"] = {"value": None, "unit": "frames/s", "cores": 0, "kind": "port",
+                                        "sample": "failed: %s: %s" % (type(e).__name__, e)}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
