@@ -54,6 +54,29 @@ def main():
             "issue_active_pct": float(d["smsp__issue_active.avg.pct_of_peak_sustained_active"]),
             "lsu_wavefronts_per_frame": float(d.get("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "0").replace(",", "")) / FRAMES,
         }
+    ll = os.path.join(G, "%s_launches.csv" % tag)
+    if os.path.exists(ll):
+        # per-kernel totals of the launch list (bench.py --steps 2 --warmup 3 under ncu: cold-cache,
+        # serialised, so shares of the device time, not absolutes)
+        agg, full = {}, []
+        for r in csv.reader(open(ll)):
+            if len(r) > 14 and r[0].isdigit() and r[12] == "gpu__time_duration.sum":
+                name = r[4].replace("void ", "").replace("<unnamed>::", "").split("(")[0]
+                a = agg.setdefault(name, [0, 0.0])
+                a[0] += 1
+                if "mfcc_int_fused" in name and r[8].replace(" ", "").startswith("(592,"):
+                    full.append(float(r[14].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0}.get(r[13], 1e-6))
+                a[1] += float(r[14].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0}.get(r[13], 1e-6)
+        tot = sum(v[1] for v in agg.values())
+        with open(os.path.join(P, "%s_launch_shares.txt" % tag), "w") as f:
+            f.write("# %s: kernels of this library launched by `bench.py --steps 2 --warmup 3 --e2e-clips 256 "
+                    "--stream-steps 20` under ncu (first 400 launches)\n" % tag)
+            f.write("%-40s %8s %12s %8s\n" % ("kernel", "launches", "total ms", "share"))
+            for name, (n, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+                f.write("%-40s %8d %12.3f %7.1f%%\n" % (name, n, ms, 100 * ms / tot))
+            big = sorted(full, reverse=True)[:5]
+            f.write("# the timed step of bench.py is ONE launch of mfcc_int_fused<32, 0> over 10 000 clips (100 %% of the "
+                    "step);\n# its full-size launches here took %s ms\n" % ", ".join("%.2f" % v for v in big))
     pb = os.path.join(G, "%s_pipe_bench.jsonl" % tag)
     if os.path.exists(pb):
         rows = [json.loads(l) for l in open(pb) if l.strip()]
