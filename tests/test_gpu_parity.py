@@ -228,3 +228,13 @@ def test_errors(ops):
         mfcc_b200.MFCC(nfft=256)
     with pytest.raises(ValueError):
         mfcc_b200.MFCC(nfilters=64, nceptrums=16)
+
+
+@pytest.mark.gpu
+def test_all_kernels_driver():
+    """profiles/all_kernels.py launches every kernel of the library (both filter sets, both
+    modes, streaming, stages, post-processing, the librosa set) with its own cross-checks."""
+    import os
+    import runpy
+    runpy.run_path(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                "profiles", "all_kernels.py"), run_name="__main__")
