@@ -228,6 +228,8 @@ def main():
     ap.add_argument("--clips", type=int, default=N_CLIPS, help="clips per GPU (default: configs[1])")
     ap.add_argument("--e2e-clips", type=int, default=2048)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa", action="store_true",
+                    help="do not pin the process to the GPU's local CPU cores (NUMA node)")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the fp32-mode and streaming-latency figures (rank 0, N=1 only)")
     ap.add_argument("--stream-steps", type=int, default=10000)
@@ -246,6 +248,9 @@ def main():
         args.warmup = 3
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from mfcc_b200 import shard
+    all_cores = os.sched_getaffinity(0)
+    numa_cores = shard.bind_to_gpu_numa(dev) if not args.no_numa else []
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -377,7 +382,8 @@ def main():
                        "clips_per_gpu": args.clips, "frames_per_step_per_gpu": frames_rank,
                        "l2": "inputs (%.1f GB per step) larger than L2, no flush needed"
                              % (args.clips * N_SAMPLES * 2 / 1e9),
-                       "e2e_clips": ne, "e2e_steps": e_steps, "e2e_matches_device_path": e2e_ok},
+                       "e2e_clips": ne, "e2e_steps": e_steps, "e2e_matches_device_path": e2e_ok,
+                       "host_cores_bound_to_gpu_numa": len(numa_cores)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
@@ -410,6 +416,7 @@ def main():
             line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             try:
+                os.sched_setaffinity(0, all_cores)      # the CPU baseline gets every host core back
                 from oracle import ref_c as RC
                 thr = RC.max_threads()
                 ncl = min(256, 16 * thr)        # ~20 core-seconds of CPU work

@@ -68,6 +68,33 @@ def split_long_clip(n_samples: int, parts: int, nfft: int = 512, hop: int = 170)
     return out
 
 
+def bind_to_gpu_numa(device) -> list:
+    """Pin this process to the CPU cores NVML reports as local to `device` (its NUMA
+    node), so that pinned staging buffers allocated afterwards are first-touched on the
+    memory next to the GPU's PCIe root port.  With one process per GPU on a two-socket box
+    this keeps host->device copies off the inter-socket link.  Returns the cores used, or
+    [] when NVML or the affinity call is unavailable (nothing is changed then)."""
+    import os
+    try:
+        import pynvml
+        dev = torch.device(device)
+        pr = torch.cuda.get_device_properties(dev)
+        pynvml.nvmlInit()
+        bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cores = [64 * w + b for w in range(words) for b in range(64) if (int(mask[w]) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cores = sorted(c for c in cores if c in allowed)
+        if not cores:
+            return []
+        os.sched_setaffinity(0, cores)
+        return cores
+    except Exception:       # noqa: BLE001 - an optimisation, never a requirement
+        return []
+
+
 def barrier(device=None):
     r, w = world()
     if w > 1:
