@@ -112,3 +112,67 @@ def test_convert_dir_librosa_writes_spec_and_sklearn(tmp_path, wav):
             assert np.abs(got - tr).max() <= 1
     assert 1 + 16000 // 170 == 95
     assert not os.path.exists(str(tmp_path / "top_level_is_not_globbed.spec"))
+
+
+# ---------------------------------------------------------------- the reference's own tool
+from oracle import ref_wav2mfcc as RW  # noqa: E402
+
+needs_ref_tool = pytest.mark.skipif(not RW.available(), reason="oracle/_ref not built and /root/reference absent")
+
+
+def _tool_clips(wav):
+    rng = np.random.default_rng(21)
+    return {"s/one.wav": wav[:4000], "s/two.wav": wav[40000:40000 + 512 + 170 * 9],     # ends on a round boundary
+            "t/u/short.wav": wav[:300], "t/exact.wav": wav[1000:1000 + 512],
+            "t/noise.wav": rng.integers(-32768, 32768, 2777).astype(np.int16)}
+
+
+def _run_reference_tool(root, wav):
+    from oracle import ref_c as RC
+    cfg = RC.RefConfig(nfilters=32, nceptrums=32)
+    clips = _tool_clips(wav)
+    for rel, x in clips.items():
+        os.makedirs(os.path.dirname(os.path.join(root, rel)), exist_ok=True)
+        write_wav(os.path.join(root, rel), x)
+    model = RW.FpgaModel(lambda s, k: RC.run(cfg, s, n_frames=k))
+    assert RW.run_tool(root, model) == 0
+    return clips, model, cfg
+
+
+@needs_ref_tool
+def test_reference_tool_agrees_with_restated_protocol(tmp_path, wav):
+    """software/main.c itself (compiled, USB replaced by a model of the FPGA top backed by
+    the C oracle) writes the .mfcc files; the restated host protocol (oracle/ref_host.py)
+    and the frame-count formula must give the same bytes."""
+    from oracle import ref_c as RC
+    clips, model, cfg = _run_reference_tool(str(tmp_path), wav)
+    assert model.resets == 1 + len(clips)                     # mfcc_open + one per file (main.c:45, :112)
+    rounds = 0
+    for rel, x in clips.items():
+        got = np.fromfile(str(tmp_path / rel)[:-3] + "mfcc", dtype=np.int16).reshape(-1, 32)
+        want = H.wav2mfcc(x, lambda s, k: RC.run(cfg, s, n_frames=k))
+        assert got.shape == (MFCCConfig().num_frames_host(len(x)), 32), rel
+        assert np.array_equal(got, want), rel
+        rounds += got.shape[0]
+    assert model.words_in == model.resets + sum(512 + 170 * (MFCCConfig().num_frames_host(len(x)) - 1)
+                                                for x in clips.values())
+
+
+@needs_ref_tool
+@pytest.mark.gpu
+def test_gpu_converter_writes_the_reference_tools_files(tmp_path, wav):
+    """Same directory through software/main.c (+ oracle-backed FPGA model) and through
+    mfcc_b200.convert on the GPU: byte-identical .mfcc files."""
+    import mfcc_b200
+    ref_root, gpu_root = str(tmp_path / "ref"), str(tmp_path / "gpu")
+    clips, _model, _cfg = _run_reference_tool(ref_root, wav)
+    for rel, x in clips.items():
+        os.makedirs(os.path.dirname(os.path.join(gpu_root, rel)), exist_ok=True)
+        write_wav(os.path.join(gpu_root, rel), x)
+    op = mfcc_b200.MFCC(nfilters=32, nceptrums=32, device="cuda:0")
+    done, rejected = convert.convert_dir(gpu_root, op=op)
+    assert len(done) == len(clips) and not rejected
+    for rel in clips:
+        a = open(os.path.join(ref_root, rel)[:-3] + "mfcc", "rb").read()
+        b = open(os.path.join(gpu_root, rel)[:-3] + "mfcc", "rb").read()
+        assert a == b and len(a) > 0, rel
