@@ -136,6 +136,15 @@ int  mfcc_b200_stage(void *handle, int32_t stage, const void *d_in, void *d_out,
                      int64_t n_frames, int32_t prev, void *stream);
 
 /*
+ * Frame with any parameter set (mfcc/core/frame.py:49-60; the constructor defaults and the
+ * reference's own bench use windowlen 400, stepsize 160, nfft 512, frame.py:50, :233-249):
+ * d_out[k][j] = d_in[stepsize*k + j] for j < windowlen, 0 for windowlen <= j < nfft and for
+ * samples at or beyond n.  Needs no handle.
+ */
+int  mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_frames, int32_t windowlen,
+                     int32_t stepsize, int32_t nfft, void *stream);
+
+/*
  * Streaming: one hop per stream per call, the mic2mfcc use of the core
  * (mfcc/targets/mic2mfcc.py:19-30).  d_state holds, per stream, the last nfft-hop
  * raw samples and the sample before them (what Preemph.odata and the Frame ring

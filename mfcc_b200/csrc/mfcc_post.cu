@@ -115,6 +115,20 @@ __global__ void k_to_int16(const float *in, int16_t *out, long long total) {
         out[i] = trunc16((double)in[i]);
 }
 
+// Frame(width, windowlen, stepsize, nfft), mfcc/core/frame.py:49-155, any parameter set:
+// frame k = y[stepsize k .. stepsize k + windowlen) followed by nfft - windowlen zeros
+// (the `padding` mux, frame.py:77, :120); samples past the end of the stream read as zero
+__global__ void k_frame_general(const int16_t *y, int16_t *fr, long long n, long long n_frames, int windowlen,
+                                int stepsize, int nfft) {
+    const long long total = n_frames * nfft;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long k = i / nfft;
+        const int j = (int)(i - k * nfft);
+        const long long s = k * stepsize + j;
+        fr[i] = (j < windowlen && s < n) ? y[s] : (int16_t)0;
+    }
+}
+
 inline int grid_for(long long total, int block) {
     long long g = (total + block - 1) / block;
     if (g > 148 * 16) g = 148 * 16;
@@ -139,6 +153,19 @@ int mfcc_b200_lifter(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_
     if (n_rows == 0) return MFCC_B200_OK;
     if (!d_in || !d_out || !d_lift) return fail_ext(MFCC_B200_EINVAL, "null buffer");
     k_lifter<<<grid_for(n_rows * ncoeff, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n_rows * ncoeff, ncoeff, d_lift);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_frames, int32_t windowlen,
+                    int32_t stepsize, int32_t nfft, void *stream)
+{
+    if (n < 0 || n_frames < 0) return fail_ext(MFCC_B200_EINVAL, "negative size");
+    if (windowlen < 1 || stepsize < 1 || nfft < windowlen) return fail_ext(MFCC_B200_EINVAL, "need 1 <= windowlen <= nfft, stepsize >= 1");
+    if (n_frames == 0) return MFCC_B200_OK;
+    if (!d_out || (n > 0 && !d_in)) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_frame_general<<<grid_for(n_frames * nfft, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n, n_frames, windowlen,
+                                                                                    stepsize, nfft);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
 }

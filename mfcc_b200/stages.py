@@ -66,31 +66,40 @@ class Preemph(_Stage):
 
 
 class Frame(_Stage):
-    """Frame(width=16, windowlen=400, stepsize=160, nfft=512), mfcc/core/frame.py:49-60.
-    int16 [N] -> int16 [K, nfft]; K = full frames unless n_frames is given (zero-extended)."""
+    """Frame(width=16, windowlen=400, stepsize=160, nfft=512), mfcc/core/frame.py:49-60, any
+    parameter set: int16 [N] -> int16 [K, nfft], frame k = y[stepsize*k : stepsize*k +
+    windowlen] then nfft - windowlen zeros.  K = full frames unless n_frames is given (the
+    stream is then zero-extended, as the reference's hosts do)."""
     stage_id = _lib.STAGE_FRAME
 
     def __init__(self, width=16, windowlen=400, stepsize=160, nfft=512, _handle=None, device=None):
         if windowlen > nfft:
             raise ValueError("windowlen must be <= nfft")          # frame.py:51
-        if (width, windowlen, stepsize, nfft) != (16, 512, 170, 512):
-            raise ValueError("CUDA path covers Frame(16, 512, 170, 512) (mfcc.py:41-44)")
+        if width != 16:
+            raise ValueError("width must be 16")
+        if windowlen < 1 or stepsize < 1:
+            raise ValueError("windowlen and stepsize must be >= 1")
         self.width, self.windowlen, self.stepsize, self.nfft = width, windowlen, stepsize, nfft
-        self._setup(_handle, device)
+        if not torch.cuda.is_available():
+            raise RuntimeError("stage operators need a CUDA device: there is no CPU fallback")
+        self.device = torch.device(device if device is not None else
+                                   "cuda:%d" % torch.cuda.current_device())
 
     def __call__(self, y, n_frames=None):
         if y.dim() != 1:
             raise ValueError("Frame takes one stream [N]")
         y = self._check(y, torch.int16, (y.shape[-1],))
         n = y.numel()
-        k = (0 if n < self.nfft else (n - self.nfft) // self.stepsize + 1) if n_frames is None \
+        k = (0 if n < self.windowlen else (n - self.windowlen) // self.stepsize + 1) if n_frames is None \
             else int(n_frames)
         out = torch.empty((k, self.nfft), dtype=torch.int16, device=self.device)
         if k == 0:
             return out
-        if n == 0:
-            return out.zero_()
-        return self._run(y, out, n, k)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_frame(
+                C.c_void_p(y.data_ptr() if n else 0), C.c_void_p(out.data_ptr()), n, k, self.windowlen,
+                self.stepsize, self.nfft, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class WindowHamming(_Stage):

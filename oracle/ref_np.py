@@ -52,20 +52,24 @@ def num_frames(n, nfft=512, hop=170):
     return 0 if n < nfft else (n - nfft) // hop + 1
 
 
-def frame(y, nfft=512, hop=None, n_frames=None):
-    """Frame(windowlen=nfft, stepsize=nfft//3, nfft), mfcc/core/frame.py:49-155 as
-    instantiated at mfcc/core/mfcc.py:41-44: frame k is y[hop*k : hop*k+nfft].
-    With n_frames given, the stream is extended with zeros (what the reference
-    hosts feed after the end of the audio: mfcc/core/mfcc.py:150-153,
-    software/main.c:135-144)."""
+def frame(y, nfft=512, hop=None, n_frames=None, windowlen=None):
+    """Frame(windowlen, stepsize, nfft), mfcc/core/frame.py:49-155: frame k is
+    y[hop*k : hop*k+windowlen] followed by nfft-windowlen zeros (the `padding` mux,
+    frame.py:77, :120).  MFCC instantiates it with windowlen = nfft, stepsize = nfft//3
+    (mfcc/core/mfcc.py:41-44), the defaults here.  With n_frames given, the stream is
+    extended with zeros (what the reference hosts feed after the end of the audio:
+    mfcc/core/mfcc.py:150-153, software/main.c:135-144)."""
     y = np.asarray(y, dtype=np.int64)
     hop = nfft // 3 if hop is None else hop
-    k = num_frames(len(y), nfft, hop) if n_frames is None else n_frames
-    need = hop * (k - 1) + nfft if k > 0 else 0
+    wl = nfft if windowlen is None else windowlen
+    k = num_frames(len(y), wl, hop) if n_frames is None else n_frames
+    need = hop * (k - 1) + wl if k > 0 else 0
     if need > len(y):
         y = np.concatenate([y, np.zeros(need - len(y), dtype=np.int64)])
-    idx = hop * np.arange(k)[:, None] + np.arange(nfft)[None, :]
-    return y[idx] if k else np.zeros((0, nfft), dtype=np.int64)
+    out = np.zeros((k, nfft), dtype=np.int64)
+    if k:
+        out[:, :wl] = y[hop * np.arange(k)[:, None] + np.arange(wl)[None, :]]
+    return out
 
 
 # ----------------------------------------------------------------------------- a3

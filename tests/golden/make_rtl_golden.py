@@ -275,8 +275,83 @@ def stage_vectors():
     return out
 
 
+def frame_vectors():
+    """Frame and Preemph on their own, for the parameter sets the reference itself uses:
+    the constructor defaults and bench case of frame.py:50, :233-249 (400/160/512), the
+    MFCC instance (512/170/512, mfcc.py:41-44), and two small ones; random gaps on the
+    sink and random stalls on the source (the five back-pressure scenarios of
+    frame.py:160-231 in one)."""
+    with contextlib.redirect_stdout(io.StringIO()):
+        from mfcc.core.frame import Frame
+        from mfcc.core.preemph import Preemph
+    rng = np.random.default_rng(11)
+    out = {}
+    for name, (wl, st, nfft, nfr) in {"400_160_512": (400, 160, 512, 6), "512_170_512": (512, 170, 512, 4),
+                                      "96_96_128": (96, 96, 128, 5), "100_30_128": (100, 30, 128, 9)}.items():
+        n = wl + st * (nfr - 1) + 7
+        x = rng.integers(-32768, 32768, n)
+        dut = Frame(16, wl, st, nfft)
+        sim = Simulator(dut)
+        rows, cur = [], []
+        gaps = np.random.default_rng(5)
+
+        def bench():
+            idx = 0
+            while len(rows) < nfr:
+                v = idx < n and gaps.random() < 0.7
+                yield dut.sink.valid.eq(int(v))
+                if v:
+                    yield dut.sink.data.eq(int(x[idx]))
+                yield dut.source.ready.eq(int(gaps.random() < 0.8))
+                took = (yield dut.sink.valid) and (yield dut.sink.ready)
+                if (yield dut.source.valid) and (yield dut.source.ready):
+                    cur.append((yield dut.source.data))
+                    if (yield dut.source.last):
+                        rows.append(list(cur))
+                        del cur[:]
+                yield
+                if took:
+                    idx += 1
+        sim.add_clock(1e-6)
+        sim.add_sync_process(bench)
+        sim.run()
+        out["frame_%s_in" % name] = x
+        out["frame_%s_out" % name] = np.array(rows, dtype=np.int64)
+    # Preemph: full-scale corners then random
+    x = np.concatenate([[32767, -32768, -32768, 32767, 32767, 0, -1, 1, 31, 32, 33, -31, -32, -33],
+                        rng.integers(-32768, 32768, 200)])
+    dut = Preemph(16)
+    sim = Simulator(dut)
+    got = []
+
+    def pbench():
+        idx = 0
+        yield dut.source.ready.eq(1)
+        while len(got) < len(x):
+            yield dut.sink.valid.eq(int(idx < len(x)))
+            if idx < len(x):
+                yield dut.sink.data.eq(int(x[idx]))
+            took = (yield dut.sink.valid) and (yield dut.sink.ready)
+            if (yield dut.source.valid) and (yield dut.source.ready):
+                got.append((yield dut.source.data))
+            yield
+            if took:
+                idx += 1
+    sim.add_clock(1e-6)
+    sim.add_sync_process(pbench)
+    sim.run()
+    out["preemph_in"] = x
+    out["preemph_out"] = np.array(got, dtype=np.int64)
+    return out
+
+
 def main():
     only = sys.argv[1:]
+    if only == ["frames"]:
+        fv = frame_vectors()
+        np.savez_compressed(os.path.join(HERE, "rtl_frame_vectors.npz"), **fv)
+        print("frame vectors:", {k: v.shape for k, v in fv.items()})
+        return
     for name, (x, nfr, nf, nc, stall) in case_inputs().items():
         if only and name not in only:
             continue
@@ -291,6 +366,9 @@ def main():
         sv = stage_vectors()
         np.savez_compressed(os.path.join(HERE, "rtl_stage_vectors.npz"), **sv)
         print("stage vectors:", {k: v.shape for k, v in sv.items()})
+        fv = frame_vectors()
+        np.savez_compressed(os.path.join(HERE, "rtl_frame_vectors.npz"), **fv)
+        print("frame vectors:", {k: v.shape for k, v in fv.items()})
 
 
 if __name__ == "__main__":

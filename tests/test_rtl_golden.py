@@ -13,7 +13,7 @@ from oracle import ref_np as R
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = os.path.join(HERE, "golden")
 CASES = sorted(os.path.basename(p)[4:-4] for p in glob.glob(os.path.join(GOLD, "rtl_*.npz"))
-               if not p.endswith("rtl_stage_vectors.npz"))
+               if not p.endswith(("rtl_stage_vectors.npz", "rtl_frame_vectors.npz")))
 
 
 def load(case):
@@ -185,3 +185,51 @@ def test_cuda_stage_operators_match_rtl_stage_vectors(sv):
     p[0, :len(sv["power_in"])] = sv["power_in"]
     got = M.PowerSpectrum(16, 30, device=dev)(T(p, np.int16)).cpu().numpy().view(np.uint32)
     assert np.array_equal(got[0, :len(sv["power_out"])], sv["power_out"])
+
+
+# ---------------------------------------------------------------- Frame / Preemph on their own
+FRAME_SETS = {"400_160_512": (400, 160, 512), "512_170_512": (512, 170, 512),
+              "96_96_128": (96, 96, 128), "100_30_128": (100, 30, 128)}
+
+
+@pytest.fixture(scope="module")
+def fvec():
+    return np.load(os.path.join(GOLD, "rtl_frame_vectors.npz"))
+
+
+@pytest.mark.parametrize("name", sorted(FRAME_SETS))
+def test_oracle_frame_matches_rtl(fvec, name):
+    """Frame(16, windowlen, stepsize, nfft) of the reference, run under random back-pressure
+    (tests/golden/make_rtl_golden.py frame_vectors): the constructor defaults / bench case
+    400-160-512 (frame.py:50, :233-249), MFCC's 512-170-512, and two small sets."""
+    wl, st, nfft = FRAME_SETS[name]
+    x, want = fvec["frame_%s_in" % name], fvec["frame_%s_out" % name]
+    got = R.frame(x, nfft=nfft, hop=st, n_frames=want.shape[0], windowlen=wl)
+    assert np.array_equal(got, want)
+    assert R.frame(x, nfft=nfft, hop=st, windowlen=wl).shape[0] == (len(x) - wl) // st + 1
+
+
+def test_oracle_preemph_matches_rtl(fvec):
+    assert np.array_equal(R.preemph(fvec["preemph_in"]), fvec["preemph_out"])
+
+
+@pytest.mark.gpu
+def test_cuda_frame_and_preemph_match_rtl(fvec):
+    import torch
+    import mfcc_b200
+    for name, (wl, st, nfft) in FRAME_SETS.items():
+        x, want = fvec["frame_%s_in" % name], fvec["frame_%s_out" % name]
+        op = mfcc_b200.Frame(16, wl, st, nfft, device="cuda:0")
+        xd = torch.from_numpy(x.astype(np.int16)).to("cuda:0")
+        got = op(xd, n_frames=want.shape[0]).cpu().numpy()
+        assert np.array_equal(got, want), name
+        full = op(xd).cpu().numpy()                            # K = full frames of the stream
+        assert full.shape == ((len(x) - wl) // st + 1, nfft) and np.array_equal(full[:want.shape[0]], want)
+        ext = op(xd, n_frames=full.shape[0] + 3).cpu().numpy()  # zero-extended tail
+        assert np.array_equal(ext, R.frame(x, nfft=nfft, hop=st, n_frames=full.shape[0] + 3, windowlen=wl))
+    assert mfcc_b200.Frame(device="cuda:0").windowlen == 400    # the reference's defaults construct
+    with pytest.raises(ValueError):
+        mfcc_b200.Frame(16, 513, 170, 512, device="cuda:0")     # frame.py:51
+    pre = mfcc_b200.Preemph(16, device="cuda:0")
+    got = pre(torch.from_numpy(fvec["preemph_in"].astype(np.int16)).to("cuda:0")).cpu().numpy()
+    assert np.array_equal(got, fvec["preemph_out"])
