@@ -5,11 +5,14 @@
 //  10*log10 with an 80 dB floor under the clip's maximum, orthonormal DCT-II).
 //
 // Two kernels, because the dB floor depends on the maximum over the whole clip:
-//   lr_logmel  one CTA per frame at a time (persistent, grid-stride over clip*frame):
-//              2048 real samples -> packed 1024-point complex FFT (5 radix-4 Stockham
-//              passes in shared memory) -> real-FFT split + |X|^2 -> sparse mel filters ->
-//              10*log10 -> workspace, clip maximum by atomicMax on an order-preserving key
-//   lr_dct     one warp per frame: clamp to max - top_db, n_mfcc dot products of n_mels
+//   lr_logmel  ONE WARP = ONE FRAME (persistent CTAs of 8 warps).  The 2048 real samples
+//              are packed into 1024 complex values and transformed as 32 x 32: every lane
+//              runs a 32-point FFT in registers, the warp transposes once through shared
+//              memory (with the W1024 twiddles applied on the way), every lane runs a
+//              second 32-point FFT.  Real-FFT split + |X|^2, sparse mel filters (four per
+//              lane), 10*log10 -> workspace; clip maximum by atomicMax on an
+//              order-preserving key.  No block-wide barrier in the frame loop.
+//   lr_dct     one warp per four frames: clamp to max - top_db, n_mfcc dot products of n_mels
 // Float32 throughout (librosa computes the STFT in complex64 for float32 audio).
 #include <cstdint>
 #include <cstring>
@@ -32,32 +35,34 @@ namespace {
 constexpr int LR_NFFT = 2048;
 constexpr int LR_HALF = LR_NFFT / 2;          // length of the packed complex transform
 constexpr int LR_BINS = LR_HALF + 1;          // 1025 real-spectrum bins
-constexpr int LR_THREADS = 256;               // one radix-4 butterfly per thread and pass
+constexpr int LR_WARPS = 8;                   // frames in flight per CTA
+constexpr int LR_THREADS = 32 * LR_WARPS;
+constexpr int LR_ROW = 33;                    // row pitch of the transposition buffer (float2)
+constexpr int LR_WBUF = 32 * LR_ROW;          // float2 per warp: transposition, spectrum, power
 constexpr int LR_MAX_MELS = 128;
 constexpr int LR_MAX_MFCC = 64;
+constexpr int LR_SLOTS = 4;                   // mel filters per lane
 
 struct LrDev {                                 // device-resident tables of one handle
     float *window;                             // [2048], includes the 1/32768 input scale
-    float2 *twp;                               // [3][340] per-pass twiddles, see LrSmem
+    float2 *tw32x32;                           // [k1][lane] = exp(-2 pi i k1 lane / 1024)
     float2 *tw2048;                            // [513]  exp(-2 pi i k / 2048)
-    int *mel_id, *mel_base;                    // [2][64] filter of thread group g in round 0 / 1 (-1: none), its first bin
-    float *melT;                               // [mel_r0 + mel_r1][256] weight of each thread at each step
-    int mel_r0, mel_r1;                        // steps of round 0 / 1 (longest span / 4, rounded up)
+    int *mel_id, *mel_base;                    // [4][32] filter of lane l in slot s (-1: none), its first bin
+    float *melT;                               // [steps][32] weight of each lane at each step
+    int mel_steps[LR_SLOTS];                   // steps of each slot (longest span in the slot)
     float *dct;                                // [n_mels][n_mfcc] (transposed for the lanes)
-};
-
-constexpr int LR_TWP = 340;                    // 4 + 16 + 64 + 256 twiddles per multiple r = 1..3
-constexpr int LR_BUF = 1280;                   // 1024 values + room for the padded layouts
-
-struct LrSmem {                                // followed by the mel weight table (dynamic)
-    float2 a[LR_BUF];
-    float2 b[LR_BUF];
-    float2 twp[3 * LR_TWP];                    // per pass, contiguous in k: W^(k r 256/NS)
-    float red[8];
 };
 
 __device__ __forceinline__ float2 cmul(float2 x, float2 w) {
     return make_float2(x.x * w.x - x.y * w.y, x.x * w.y + x.y * w.x);
+}
+
+// low half of a word as a signed value: one PRMT in sign-replicate mode (the intrinsic
+// __byte_perm masks that selector bit off)
+__device__ __forceinline__ int sext16(int w) {
+    int r;
+    asm("prmt.b32 %0, %1, 0, 0x9910;" : "=r"(r) : "r"(w));
+    return r;
 }
 
 // numpy.pad(mode="reflect") index map, any number of folds
@@ -78,100 +83,119 @@ __device__ __forceinline__ float key_float(int k) {
     return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff);
 }
 
-// Buffer layouts: value i lives at i + C*(i >> 4).  Any C keeps the contiguous reads of
-// the next pass conflict-free (aligned runs of 16 stay contiguous); C = 1 spreads the
-// stride-4 stores of the first pass over all banks, C = 4 those of the second pass.
-template <int C>
-__device__ __forceinline__ int padi(int i) { return C ? i + C * (i >> 4) : i; }
+// cos(pi k / 16), -8 <= k <= 16; no recursion and forced inlining, so that with the loops
+// below unrolled every use folds to a literal operand
+__device__ __forceinline__ constexpr float cos16(int k) {
+    const int a = k < 0 ? -k : k;
+    const int r = a > 8 ? 16 - a : a;
+    const float c = r == 0 ? 1.0f
+                  : r == 1 ? 0.98078528040323044913f
+                  : r == 2 ? 0.92387953251128675613f
+                  : r == 3 ? 0.83146961230254523708f
+                  : r == 4 ? 0.70710678118654752440f
+                  : r == 5 ? 0.55557023301960222474f
+                  : r == 6 ? 0.38268343236508977173f
+                  : r == 7 ? 0.19509032201612826785f
+                  : 0.0f;
+    return a > 8 ? -c : c;
+}
+__host__ __device__ constexpr int brev5(int v) {
+    return ((v & 1) << 4) | ((v & 2) << 2) | (v & 4) | ((v & 8) >> 2) | ((v & 16) >> 4);
+}
 
-__host__ __device__ constexpr int lr_tw_off(int ns) { return ns == 4 ? 0 : ns == 16 ? 4 : ns == 64 ? 20 : 84; }
-
-// One radix-4 Stockham pass: thread j combines in[j + 256 r], r = 0..3, with twiddles
-// exp(-2 pi i k r / (4 NS)), k = j mod NS, into out[4 (j - k) + k + r NS].  All eight
-// addresses are one base per side plus constants (the padded layouts keep that true).
-template <int NS, int CIN, int COUT>
-__device__ __forceinline__ void stockham_pass(const float2 *__restrict__ in, float2 *__restrict__ out,
-                                              const float2 *__restrict__ twp, int j) {
-    const int k = j & (NS - 1);
-    const float2 *ip = in + padi<CIN>(j);
-    constexpr int IS = 256 + 16 * CIN;                       // (j + 256 r) >> 4 = (j >> 4) + 16 r
-    float2 u0 = ip[0], u1 = ip[IS], u2 = ip[2 * IS], u3 = ip[3 * IS];
-    if (NS > 1) {
-        const float2 *t = twp + lr_tw_off(NS) + k;
-        u1 = cmul(u1, t[0]);
-        u2 = cmul(u2, t[LR_TWP]);
-        u3 = cmul(u3, t[2 * LR_TWP]);
+// 32-point forward DFT in registers, radix-2 decimation in frequency: on return v[j] holds
+// bin brev5(j).  Twiddles are literals; W^0 and W^8 = -j cost nothing.
+__device__ __forceinline__ void fft32(float2 (&v)[32])
+{
+#pragma unroll
+    for (int h = 16; h >= 1; h >>= 1) {
+#pragma unroll
+        for (int g = 0; g < 32; g += 2 * h) {
+#pragma unroll
+            for (int k = 0; k < h; k++) {
+                const float2 a = v[g + k], b = v[g + k + h];
+                v[g + k] = make_float2(a.x + b.x, a.y + b.y);
+                const float2 d = make_float2(a.x - b.x, a.y - b.y);
+                const int e = k * (16 / h);                    // exponent of W32
+                if (e == 0) v[g + k + h] = d;
+                else if (e == 8) v[g + k + h] = make_float2(d.y, -d.x);
+                else v[g + k + h] = cmul(d, make_float2(cos16(e), -cos16(8 - e)));
+            }
+        }
     }
-    const float2 v0 = make_float2(u0.x + u2.x, u0.y + u2.y);
-    const float2 v1 = make_float2(u0.x - u2.x, u0.y - u2.y);
-    const float2 v2 = make_float2(u1.x + u3.x, u1.y + u3.y);
-    const float2 v3 = make_float2(u1.y - u3.y, u3.x - u1.x);       // -i (u1 - u3)
-    const int j0 = ((j - k) << 2) + k;
-    // NS < 16: the four outputs share one 16-group, so the pad term is that of j0
-    float2 *op = out + (NS >= 16 ? padi<COUT>(j0) : j0 + COUT * (j0 >> 4));
-    constexpr int OS = NS >= 16 ? NS + COUT * (NS / 16) : NS;
-    op[0] = make_float2(v0.x + v2.x, v0.y + v2.y);
-    op[OS] = make_float2(v1.x + v3.x, v1.y + v3.y);
-    op[2 * OS] = make_float2(v0.x - v2.x, v0.y - v2.y);
-    op[3 * OS] = make_float2(v1.x - v3.x, v1.y - v3.y);
+}
+
+// Shared memory of lr_logmel (dynamic): [tw32x32 1024][tw2048 520] float2, then the mel
+// weight table [steps][32] float, then one LR_WBUF float2 buffer per warp.
+constexpr int LR_TW2048_PAD = 520;
+__host__ __device__ constexpr size_t lr_smem_bytes(int steps) {
+    return (size_t)(1024 + LR_TW2048_PAD) * sizeof(float2) + (size_t)steps * 32 * sizeof(float) +
+           (size_t)LR_WARPS * LR_WBUF * sizeof(float2);
 }
 
 // d_x [n_clips][clip_stride] int16; logmel [n_clips][n_frames][n_mels]; clipmax [n_clips] keys
-// TR0/TR1: compile-time mel step counts (0 = take them from the tables at run time)
-template <int TR0, int TR1>
-__global__ void __launch_bounds__(LR_THREADS, 4)
+// FIXED: the mel step counts are the default bank's (6, 10, 22, 48: 128 Slaney filters at
+// 16 kHz), known at compile time and fully unrolled; otherwise they come from the tables.
+__host__ __device__ constexpr int lr_def_steps(int s) { return s == 0 ? 6 : s == 1 ? 10 : s == 2 ? 22 : 48; }
+template <bool FIXED>
+__global__ void __launch_bounds__(LR_THREADS, 2)
 lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_samples, int n_clips,
           long long n_frames, int hop, int center, int n_mels, float amin, LrDev t,
           float *__restrict__ logmel, int *__restrict__ clipmax, float *__restrict__ power_tap)
 {
     extern __shared__ __align__(16) unsigned char lr_smem_raw[];
-    LrSmem &sm = *reinterpret_cast<LrSmem *>(lr_smem_raw);
-    float *wT = reinterpret_cast<float *>(lr_smem_raw + sizeof(LrSmem));    // [R0 + R1][256]
-    const int tid = threadIdx.x;
-    const int R0 = TR0 ? TR0 : t.mel_r0, R1 = TR1 ? TR1 : t.mel_r1;
-    for (int i = tid; i < 3 * LR_TWP; i += LR_THREADS) sm.twp[i] = t.twp[i];
-    for (int i = tid; i < (R0 + R1) * LR_THREADS; i += LR_THREADS) wT[i] = t.melT[i];
+    float2 *tw = reinterpret_cast<float2 *>(lr_smem_raw);              // [k1][lane]
+    float2 *tw2 = tw + 1024;                                           // exp(-2 pi i k / 2048)
+    float *wT = reinterpret_cast<float *>(tw2 + LR_TW2048_PAD);        // [step][lane]
+    const int steps = t.mel_steps[0] + t.mel_steps[1] + t.mel_steps[2] + t.mel_steps[3];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float2 *buf = reinterpret_cast<float2 *>(wT + steps * 32) + warp * LR_WBUF;
+    float *pw = reinterpret_cast<float *>(buf);                        // [1025] after the split
+
+    for (int i = tid; i < 1024; i += LR_THREADS) tw[i] = t.tw32x32[i];
+    for (int i = tid; i < 513; i += LR_THREADS) tw2[i] = t.tw2048[i];
+    for (int i = tid; i < steps * 32; i += LR_THREADS) wT[i] = t.melT[i];
     // the mel walk reads a few zero-weighted words past bin 1024: they must be finite
-    for (int i = tid; i < LR_BUF; i += LR_THREADS) sm.a[i] = sm.b[i] = make_float2(0.0f, 0.0f);
+    for (int i = lane; i < LR_WBUF; i += 32) buf[i] = make_float2(0.0f, 0.0f);
     __syncthreads();
-    float *pw = reinterpret_cast<float *>(sm.a);               // [1025] after the transform
 
-    // frame-invariant per-thread values: window pairs, split twiddles, mel assignment
-    float2 win[4], tws[2];
+    // frame-invariant per-lane values: the four mel filters of this lane
+    int mid[LR_SLOTS], mlo[LR_SLOTS];
 #pragma unroll
-    for (int r = 0; r < 4; r++) win[r] = __ldg(reinterpret_cast<const float2 *>(t.window) + tid + 256 * r);
-#pragma unroll
-    for (int r = 0; r < 2; r++) tws[r] = __ldg(t.tw2048 + tid + 256 * r);
-    const int grp = tid >> 2, q = tid & 3;
-    const int m0 = __ldg(t.mel_id + grp), m1 = __ldg(t.mel_id + 64 + grp);       // -1: none
-    const float *pw0 = pw + __ldg(t.mel_base + grp) + q, *pw1 = pw + __ldg(t.mel_base + 64 + grp) + q;
-    const float *wT0 = wT + tid, *wT1 = wT + R0 * LR_THREADS + tid;
-
+    for (int s = 0; s < LR_SLOTS; s++) {
+        mid[s] = __ldg(t.mel_id + 32 * s + lane);
+        mlo[s] = __ldg(t.mel_base + 32 * s + lane);
+    }
+    const float2 *win2 = reinterpret_cast<const float2 *>(t.window) + lane;
     // rows whose samples can be fetched as aligned pairs (frame starts are even then)
     const bool pairs = ((reinterpret_cast<uintptr_t>(d_x) & 3) == 0) && ((clip_stride & 1) == 0) &&
                        ((hop & 1) == 0);
 
-    int clip = (int)((long long)blockIdx.x / n_frames);
-    long long f = (long long)blockIdx.x - (long long)clip * n_frames;
-    while (clip < n_clips) {
-        const long long item = (long long)clip * n_frames + f;
+    const long long total = (long long)n_clips * n_frames;
+    for (long long item = (long long)blockIdx.x * LR_WARPS + warp; item < total; item += (long long)gridDim.x * LR_WARPS) {
+        const int clip = (int)(item / n_frames);
+        const long long f = item - (long long)clip * n_frames;
         const int16_t *x = d_x + (long long)clip * clip_stride;
         const long long s0 = f * hop - (center ? LR_HALF : 0);
 
-        // windowed samples, even/odd packed: z[n] = (y[2n] w[2n], y[2n+1] w[2n+1])
+        // lane L takes z[L + 32 i], z[n] = (y[2n] w[2n], y[2n+1] w[2n+1]): coalesced 128-byte rows
+        float2 v[32];
         const bool inside = s0 >= 0 && s0 + LR_NFFT <= n_samples;
         if (inside && pairs) {
-            const int *xp = reinterpret_cast<const int *>(x + s0) + tid;
+            const int *xp = reinterpret_cast<const int *>(x + s0) + lane;
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const int v = __ldg(xp + 256 * r);
-                sm.a[tid + 256 * r] = make_float2((float)(short)(v & 0xffff) * win[r].x, (float)(v >> 16) * win[r].y);
+            for (int i = 0; i < 32; i++) {
+                const int s = __ldg(xp + 32 * i);
+                const float2 w = __ldg(win2 + 32 * i);
+                // low half sign-extended by one PRMT (an I2F.S16 would go through the slow conversion pipe)
+                v[i] = make_float2((float)sext16(s) * w.x, (float)(s >> 16) * w.y);
+                if ((i & 7) == 7) __syncwarp();                 // keeps at most 8 rows of loads in flight (registers)
             }
         } else {
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const int n = tid + 256 * r;
-                const long long i0 = s0 + 2 * n, i1 = i0 + 1;
+            // frames that touch the padding (or unaligned rows): staged through the warp's
+            // buffer so that v[] keeps compile-time indices
+            for (int i = 0; i < 32; i++) {
+                const long long i0 = s0 + 2 * (lane + 32 * i), i1 = i0 + 1;
                 float y0, y1;
                 if (inside) {
                     y0 = (float)x[i0];
@@ -183,104 +207,149 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
                     y0 = i0 < n_samples ? (float)x[i0] : 0.0f;
                     y1 = i1 < n_samples ? (float)x[i1] : 0.0f;
                 }
-                sm.a[n] = make_float2(y0 * win[r].x, y1 * win[r].y);
+                const float2 w = __ldg(win2 + 32 * i);
+                buf[lane + 32 * i] = make_float2(y0 * w.x, y1 * w.y);
             }
-        }
-        __syncthreads();
-        stockham_pass<1, 0, 1>(sm.a, sm.b, sm.twp, tid);
-        __syncthreads();
-        stockham_pass<4, 1, 4>(sm.b, sm.a, sm.twp, tid);
-        __syncthreads();
-        stockham_pass<16, 4, 0>(sm.a, sm.b, sm.twp, tid);
-        __syncthreads();
-        stockham_pass<64, 0, 0>(sm.b, sm.a, sm.twp, tid);
-        __syncthreads();
-        stockham_pass<256, 0, 0>(sm.a, sm.b, sm.twp, tid);
-        __syncthreads();
-
-        // real-FFT split: X[k] = F + W^k G, X[1024-k] = conj(F - W^k G); power into pw (= sm.a)
 #pragma unroll
-        for (int r = 0; r < 2; r++) {
-            const int k = tid + 256 * r;
-            const float2 za = sm.b[k], zb = sm.b[(LR_HALF - k) & (LR_HALF - 1)];
+            for (int i = 0; i < 32; i++) v[i] = buf[lane + 32 * i];
+            __syncwarp();
+        }
+
+        // Z[k1 + 32 k2] = sum_L W32^(L k2) [ W1024^(L k1) sum_i z[L + 32 i] W32^(i k1) ]
+        fft32(v);                                               // over i: v[j] = Y_L[k1 = brev5(j)]
+#pragma unroll
+        for (int j = 0; j < 32; j++) {
+            const int k1 = brev5(j);
+            buf[k1 * LR_ROW + lane] = k1 ? cmul(v[j], tw[k1 * 32 + lane]) : v[j];
+            if ((j & 7) == 7) __syncwarp();                     // bounds the twiddle loads in flight
+        }
+        __syncwarp();
+#pragma unroll
+        for (int L = 0; L < 32; L++) v[L] = buf[lane * LR_ROW + L];      // lane = k1, values over L
+        __syncwarp();
+        fft32(v);                                               // over L: v[j] = Z[lane + 32 brev5(j)]
+#pragma unroll
+        for (int j = 0; j < 32; j++) buf[lane + 32 * brev5(j)] = v[j];   // natural order
+        __syncwarp();
+
+        // real-FFT split: X[k] = F + W^k G, X[1024-k] = conj(F - W^k G), k = lane + 32 i < 512.
+        // Both operands are fetched before anything is written: the power goes into the same buffer.
+        float2 zc = buf[512];
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const int k = lane + 32 * i;
+            v[2 * i] = buf[k];
+            v[2 * i + 1] = buf[(LR_HALF - k) & (LR_HALF - 1)];
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const int k = lane + 32 * i;
+            const float2 za = v[2 * i], zb = v[2 * i + 1];
             const float2 F = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
             const float2 G = make_float2(0.5f * (za.y + zb.y), -0.5f * (za.x - zb.x));
-            const float2 T = cmul(G, tws[r]);
+            const float2 T = cmul(G, tw2[k]);
             const float pr = F.x + T.x, pi = F.y + T.y, qr = F.x - T.x, qi = F.y - T.y;
             pw[k] = pr * pr + pi * pi;
             pw[LR_HALF - k] = qr * qr + qi * qi;
         }
-        if (tid == 0) {                                         // k = 512: W^512 = -i
-            const float2 z = sm.b[512];
-            pw[512] = z.x * z.x + z.y * z.y;
-        }
-        __syncthreads();
+        if (lane == 0) pw[512] = zc.x * zc.x + zc.y * zc.y;     // W^512 = -i
+        __syncwarp();
         if (power_tap) {
             float *dst = power_tap + item * LR_BINS;
-            for (int k = tid; k < LR_BINS; k += LR_THREADS) dst[k] = pw[k];
+            for (int k = lane; k < LR_BINS; k += 32) dst[k] = pw[k];
         }
 
-        // mel filters: four threads share a filter (bins lo+q, lo+q+4, ...); group g takes
-        // filter g and then filter n_mels-1-g, so narrow low filters pair with wide high
-        // ones; weights sit in shared memory as [step][thread], zero beyond a filter's span
-        float a0 = 0.0f, a1 = 0.0f;
-#pragma unroll(TR0 ? TR0 : 4)
-        for (int i = 0; i < R0; i++) a0 = fmaf(wT0[i * LR_THREADS], pw0[4 * i], a0);
-#pragma unroll(TR1 ? TR1 : 4)
-        for (int i = 0; i < R1; i++) a1 = fmaf(wT1[i * LR_THREADS], pw1[4 * i], a1);
-        a0 += __shfl_xor_sync(0xffffffffu, a0, 1);
-        a1 += __shfl_xor_sync(0xffffffffu, a1, 1);
-        a0 += __shfl_xor_sync(0xffffffffu, a0, 2);
-        a1 += __shfl_xor_sync(0xffffffffu, a1, 2);
+        // mel filters: lane l owns filters l, 63-l, 64+l, 127-l (narrow ones pair with wide
+        // ones); weights sit in shared memory as [step][lane], zero beyond a filter's span
         float db = -3.0e38f;
-        {
-            float *lm = logmel + item * n_mels;
-            const float v0 = 3.0102999566398120f * __log2f(fmaxf(a0, amin));    // 10 log10
-            const float v1 = 3.0102999566398120f * __log2f(fmaxf(a1, amin));
-            if (m0 >= 0) db = v0;
-            if (m1 >= 0) db = fmaxf(db, v1);
-            if (q == 0 && m0 >= 0) lm[m0] = v0;
-            if (q == 1 && m1 >= 0) lm[m1] = v1;
+        float *lm = logmel + item * n_mels;
+        const float *w = wT + lane;
+#pragma unroll
+        for (int s = 0; s < LR_SLOTS; s++) {
+            const int n = FIXED ? lr_def_steps(s) : t.mel_steps[s];
+            const float *p = pw + mlo[s];
+            float a0 = 0.0f, a1 = 0.0f;
+            if (FIXED) {
+#pragma unroll
+                for (int i = 0; i < lr_def_steps(s); i += 2) {
+                    a0 = fmaf(w[i * 32], p[i], a0);
+                    a1 = fmaf(w[i * 32 + 32], p[i + 1], a1);       // every default count is even
+                }
+            } else {
+                int i = 0;
+                for (; i + 1 < n; i += 2) {
+                    a0 = fmaf(w[i * 32], p[i], a0);
+                    a1 = fmaf(w[i * 32 + 32], p[i + 1], a1);
+                }
+                if (i < n) a0 = fmaf(w[i * 32], p[i], a0);
+            }
+            w += n * 32;
+            if (mid[s] >= 0) {
+                const float d = 3.0102999566398120f * __log2f(fmaxf(a0 + a1, amin));     // 10 log10
+                lm[mid[s]] = d;
+                db = fmaxf(db, d);
+            }
         }
         for (int o = 16; o; o >>= 1) db = fmaxf(db, __shfl_xor_sync(0xffffffffu, db, o));
-        if ((tid & 31) == 0) sm.red[tid >> 5] = db;
-        __syncthreads();                                        // also: pw is free again
-        if (tid == 0) {
-            float v = sm.red[0];
-            for (int i = 1; i < 8; i++) v = fmaxf(v, sm.red[i]);
-            atomicMax(clipmax + clip, float_key(v));
-        }
-        f += gridDim.x;
-        if (f >= n_frames) {
-            clip += (int)(f / n_frames);
-            f %= n_frames;
-        }
+        if (lane == 0) atomicMax(clipmax + clip, float_key(db));
+        __syncwarp();                                           // pw is free again
     }
 }
 
-// logmel [n_clips][n_frames][n_mels] -> out [n_clips][n_frames][n_mfcc] (row pitch out_clip_stride)
+// logmel [n_clips][n_frames][n_mels] -> out [n_clips][n_frames][n_mfcc] (row pitch out_clip_stride).
+// One warp takes four consecutive frames at a time: their clamped log-mel rows are interleaved
+// in shared memory ([n][4], one 16-byte broadcast load per mel band), lane k accumulates
+// coefficient k of all four, so every DCT weight is loaded once per four frames.
 __global__ void __launch_bounds__(256)
 lr_dct(const float *__restrict__ logmel, const int *__restrict__ clipmax, int n_clips, long long n_frames,
        int n_mels, int n_mfcc, float top_db, LrDev t, float *__restrict__ out, long long out_clip_stride)
 {
-    extern __shared__ float dsm[];
+    extern __shared__ __align__(16) float dsm[];
     float *D = dsm;                                            // [n_mels][n_mfcc]
-    float *vbuf = dsm + n_mels * n_mfcc;                       // [8 warps][n_mels]
+    float4 *vbuf = reinterpret_cast<float4 *>(dsm + ((n_mels * n_mfcc + 3) & ~3));    // [8 warps][n_mels]
     for (int i = threadIdx.x; i < n_mels * n_mfcc; i += blockDim.x) D[i] = t.dct[i];
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float *v = vbuf + warp * n_mels;
+    float4 *v4 = vbuf + warp * n_mels;
+    float *v = reinterpret_cast<float *>(v4);
     const long long total = (long long)n_clips * n_frames;
-    for (long long item = (long long)blockIdx.x * 8 + warp; item < total; item += (long long)gridDim.x * 8) {
-        const int clip = (int)(item / n_frames);
-        const long long f = item - (long long)clip * n_frames;
-        const float floor_db = top_db >= 0.0f ? key_float(clipmax[clip]) - top_db : -3.0e38f;
-        for (int n = lane; n < n_mels; n += 32) v[n] = fmaxf(logmel[item * n_mels + n], floor_db);
+    const long long groups = (total + 3) / 4;
+    for (long long g = (long long)blockIdx.x * 8 + warp; g < groups; g += (long long)gridDim.x * 8) {
+        const long long item0 = g * 4;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const long long item = item0 + q;
+            if (item < total) {
+                const int clip = (int)(item / n_frames);
+                const float floor_db = top_db >= 0.0f ? key_float(clipmax[clip]) - top_db : -3.0e38f;
+                for (int n = lane; n < n_mels; n += 32) v[4 * n + q] = fmaxf(logmel[item * n_mels + n], floor_db);
+            } else {
+                for (int n = lane; n < n_mels; n += 32) v[4 * n + q] = 0.0f;
+            }
+        }
         __syncwarp();
         for (int k = lane; k < n_mfcc; k += 32) {
-            float acc = 0.0f;
-            for (int n = 0; n < n_mels; n++) acc = fmaf(D[n * n_mfcc + k], v[n], acc);
-            out[(long long)clip * out_clip_stride + f * n_mfcc + k] = acc;
+            float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll 8
+            for (int n = 0; n < n_mels; n++) {
+                const float d = D[n * n_mfcc + k];
+                const float4 x = v4[n];
+                acc.x = fmaf(d, x.x, acc.x);
+                acc.y = fmaf(d, x.y, acc.y);
+                acc.z = fmaf(d, x.z, acc.z);
+                acc.w = fmaf(d, x.w, acc.w);
+            }
+            const float r[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const long long item = item0 + q;
+                if (item < total) {
+                    const int clip = (int)(item / n_frames);
+                    const long long f = item - (long long)clip * n_frames;
+                    out[(long long)clip * out_clip_stride + f * n_mfcc + k] = r[q];
+                }
+            }
         }
         __syncwarp();
     }
@@ -291,10 +360,12 @@ __global__ void lr_init_max(int *clipmax, int n) {
     if (i < n) clipmax[i] = (int)0x80000000;
 }
 
+using LrLogmelFn = void (*)(const int16_t *, long long, long long, int, long long, int, int, int, float, LrDev, float *,
+                            int *, float *);
+
 struct LrHandle {
     int hop, n_mels, n_mfcc, center, sms, ctas1;
-    void (*logmel)(const int16_t *, long long, long long, int, long long, int, int, int, float, LrDev, float *, int *,
-                   float *);
+    LrLogmelFn logmel;
     size_t smem1;
     float amin, top_db;
     LrDev dev;
@@ -329,16 +400,16 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
 
     // host-side tables
     const double PI = 3.14159265358979323846;
-    std::vector<float2> tw1(3 * LR_TWP), tw2(513);
-    for (int r = 1; r <= 3; r++)
-        for (int ns = 4; ns <= 256; ns *= 4)
-            for (int k = 0; k < ns; k++) {
-                const double ang = 2 * PI * k * r / (4.0 * ns);
-                tw1[(r - 1) * LR_TWP + lr_tw_off(ns) + k] = make_float2((float)cos(ang), (float)-sin(ang));
-            }
+    std::vector<float2> tw1(1024), tw2(513);
+    for (int k1 = 0; k1 < 32; k1++)
+        for (int L = 0; L < 32; L++) {
+            const double ang = 2 * PI * (k1 * L) / 1024.0;
+            tw1[k1 * 32 + L] = make_float2((float)cos(ang), (float)-sin(ang));
+        }
     for (int k = 0; k < 513; k++) tw2[k] = make_float2((float)cos(2 * PI * k / 2048), (float)-sin(2 * PI * k / 2048));
-    // thread group g (four threads) owns filter g in round 0 and filter n_mels-1-g in round 1
-    std::vector<int> lo(cfg->n_mels), cnt(cfg->n_mels), ids(128, -1), base(128, 0);
+    // lane l owns filters l, 63-l, 64+l, 127-l (slots 0..3): narrow low filters pair with wide
+    // high ones; every slot runs as many steps as its widest filter
+    std::vector<int> lo(cfg->n_mels), cnt(cfg->n_mels), ids(LR_SLOTS * 32, -1), base(LR_SLOTS * 32, 0);
     for (int m = 0; m < cfg->n_mels; m++) {
         const float *row = cfg->mel + (size_t)m * LR_BINS;
         int a = 0, b = LR_BINS;
@@ -347,29 +418,29 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
         lo[m] = a < LR_BINS ? a : 0;
         cnt[m] = b - a;
     }
-    const int half_up = (cfg->n_mels + 1) / 2, half_dn = cfg->n_mels / 2;
-    int r0 = 0, r1 = 0;
-    for (int g = 0; g < 64; g++) {
-        if (g < half_up) { ids[g] = g; base[g] = lo[g]; r0 = std::max(r0, (cnt[g] + 3) / 4); }
-        if (g < half_dn) {
-            const int m = cfg->n_mels - 1 - g;
-            ids[64 + g] = m; base[64 + g] = lo[m]; r1 = std::max(r1, (cnt[m] + 3) / 4);
+    int steps = 0, soff[LR_SLOTS];
+    for (int s = 0; s < LR_SLOTS; s++) {
+        int n = 0;
+        for (int l = 0; l < 32; l++) {
+            const int m = s == 0 ? l : s == 1 ? 63 - l : s == 2 ? 64 + l : 127 - l;
+            if (m >= cfg->n_mels) continue;
+            ids[32 * s + l] = m;
+            base[32 * s + l] = lo[m];
+            n = std::max(n, cnt[m]);
         }
+        h->dev.mel_steps[s] = n;
+        soff[s] = steps;
+        steps += n;
     }
-    h->dev.mel_r0 = r0; h->dev.mel_r1 = r1;
-    std::vector<float> wT((size_t)std::max(1, r0 + r1) * LR_THREADS, 0.0f);
-    for (int tid = 0; tid < LR_THREADS; tid++)
-        for (int round = 0; round < 2; round++) {
-            const int m = ids[64 * round + (tid >> 2)];
+    std::vector<float> wT((size_t)std::max(1, steps) * 32, 0.0f);
+    for (int s = 0; s < LR_SLOTS; s++)
+        for (int l = 0; l < 32; l++) {
+            const int m = ids[32 * s + l];
             if (m < 0) continue;
             const float *row = cfg->mel + (size_t)m * LR_BINS;
-            const int steps = round ? r1 : r0;
-            for (int i = 0; i < steps; i++) {
-                const int bin = lo[m] + (tid & 3) + 4 * i;
-                if (bin < lo[m] + cnt[m]) wT[(size_t)((round ? r0 : 0) + i) * LR_THREADS + tid] = row[bin];
-            }
+            for (int i = 0; i < cnt[m]; i++) wT[(size_t)(soff[s] + i) * 32 + l] = row[lo[m] + i];
         }
-    h->smem1 = sizeof(LrSmem) + (size_t)(r0 + r1) * LR_THREADS * sizeof(float);
+    h->smem1 = lr_smem_bytes(steps);
     std::vector<float> dT((size_t)cfg->n_mels * cfg->n_mfcc);
     for (int k = 0; k < cfg->n_mfcc; k++)
         for (int n = 0; n < cfg->n_mels; n++) dT[(size_t)n * cfg->n_mfcc + k] = cfg->dct[(size_t)k * cfg->n_mels + n];
@@ -385,7 +456,7 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
         return p;
     };
     h->dev.window = (float *)upload(cfg->window, LR_NFFT * sizeof(float));
-    h->dev.twp = (float2 *)upload(tw1.data(), tw1.size() * sizeof(float2));
+    h->dev.tw32x32 = (float2 *)upload(tw1.data(), tw1.size() * sizeof(float2));
     h->dev.tw2048 = (float2 *)upload(tw2.data(), tw2.size() * sizeof(float2));
     h->dev.mel_id = (int *)upload(ids.data(), ids.size() * sizeof(int));
     h->dev.mel_base = (int *)upload(base.data(), base.size() * sizeof(int));
@@ -395,8 +466,9 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
         delete h;
         return fail_ext(MFCC_B200_EUNSUPPORTED, "mel filters too wide for the shared-memory weight table");
     }
-    // the default filter bank (128 Slaney filters at 16 kHz) has 3 + 12 steps: unrolled instantiation
-    h->logmel = (r0 == 3 && r1 == 12) ? lr_logmel<3, 12> : lr_logmel<0, 0>;
+    bool def = true;
+    for (int s = 0; s < LR_SLOTS; s++) def = def && h->dev.mel_steps[s] == lr_def_steps(s);
+    h->logmel = def ? lr_logmel<true> : lr_logmel<false>;
     if (e == cudaSuccess) e = cudaFuncSetAttribute(h->logmel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem1);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas1, h->logmel, LR_THREADS, h->smem1);
     if (e == cudaSuccess && h->ctas1 < 1) h->ctas1 = 1;
@@ -459,14 +531,14 @@ int mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_stride,
     lr_init_max<<<(n_clips + 255) / 256, 256, 0, st>>>(clipmax, n_clips);
     mfccb_host::count_launch();
     long long g1 = (long long)h->sms * h->ctas1;
-    if (g1 > total) g1 = total;
+    if (g1 > (total + LR_WARPS - 1) / LR_WARPS) g1 = (total + LR_WARPS - 1) / LR_WARPS;
     h->logmel<<<(unsigned)g1, LR_THREADS, h->smem1, st>>>(d_x, clip_stride, n_samples, n_clips, n_frames, h->hop, h->center,
                                                   h->n_mels, h->amin, h->dev, logmel, clipmax,
                                                   taps ? taps->d_power : nullptr);
     mfccb_host::count_launch();
-    long long g2 = (total + 7) / 8;
+    long long g2 = (total + 31) / 32;
     if (g2 > (long long)h->sms * 8) g2 = (long long)h->sms * 8;
-    const size_t dsm = ((size_t)h->n_mels * h->n_mfcc + 8 * (size_t)h->n_mels) * sizeof(float);
+    const size_t dsm = ((((size_t)h->n_mels * h->n_mfcc + 3) & ~(size_t)3) + 8 * 4 * (size_t)h->n_mels) * sizeof(float);
     lr_dct<<<(unsigned)g2, 256, dsm, st>>>(logmel, clipmax, n_clips, n_frames, h->n_mels, h->n_mfcc, h->top_db, h->dev,
                                            d_out, out_clip_stride);
     mfccb_host::count_launch();
