@@ -172,12 +172,19 @@ def run_reference(args, rank, world):
         "gpu_launches": 0}))
 
 
-def stream_latency(op, dev, n_streams=4096, steps=10000, warmup=200):
+def stream_latency(op, dev, n_streams=4096, steps=10000, warmup=200, groups=1, zero_copy=False):
     """BASELINE.json configs[4]: `n_streams` live streams, one
     170-sample hop per stream per step, the step captured once in a CUDA graph (H2D of the
     hops from pinned memory, the streaming kernel, D2H of the cepstrum columns).  Returns
     p50/p99 of the device time per step (CUDA events around the replay) and of the host
-    wall time per step (perf_counter around replay + stream synchronize)."""
+    wall time per step (perf_counter around replay + stream synchronize).
+
+    groups > 1: the streams are cut into that many groups, each a branch of the graph on its
+    own CUDA stream (copy-in, kernel, copy-out of its rows).  Measured SLOWER on B200 (2
+    groups 66-74 us, 4 groups 79 us against 63 us): per-copy latency outweighs the overlap.
+    zero_copy=True: the kernel reads the pinned hops and writes the pinned columns itself
+    (same p50, tighter p99); zero_copy="out": hops by DMA, columns written by the kernel
+    straight into pinned host memory (57 us p50: one copy operation less)."""
     import torch
     hop_h = torch.randint(-3000, 3000, (n_streams, 170), dtype=torch.int16).pin_memory()
     out_h = torch.empty((n_streams, op.nceptrums), dtype=op.out_dtype).pin_memory()
@@ -185,17 +192,39 @@ def stream_latency(op, dev, n_streams=4096, steps=10000, warmup=200):
     out_d = torch.empty((n_streams, op.nceptrums), dtype=op.out_dtype, device=dev)
     op.reset(n_streams)
     st = torch.cuda.Stream(device=dev)
-    with torch.cuda.stream(st):
-        for _ in range(3):
+    side = [torch.cuda.Stream(device=dev) for _ in range(groups)] if groups > 1 else []
+    cuts = [n_streams * i // groups for i in range(groups + 1)]
+
+    def one_step():
+        if zero_copy == "out":  # DMA the hops in, the kernel writes the columns to pinned host memory itself
+            hop_d.copy_(hop_h, non_blocking=True)
+            op.step(hop_d, out=out_h)
+            return
+        if zero_copy:           # the kernel reads the pinned hops and writes the pinned columns itself
+            op.step(hop_h, out=out_h)
+            return
+        if groups == 1:
             hop_d.copy_(hop_h, non_blocking=True)
             op.step(hop_d, out=out_d)
             out_h.copy_(out_d, non_blocking=True)
+            return
+        for i, s in enumerate(side):
+            a, b = cuts[i], cuts[i + 1]
+            s.wait_stream(st)
+            with torch.cuda.stream(s):
+                hop_d[a:b].copy_(hop_h[a:b], non_blocking=True)
+                op.step(hop_d[a:b], out=out_d[a:b], first_stream=a)
+                out_h[a:b].copy_(out_d[a:b], non_blocking=True)
+        for s in side:
+            st.wait_stream(s)
+
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            one_step()
         st.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=st):
-            hop_d.copy_(hop_h, non_blocking=True)
-            op.step(hop_d, out=out_d)
-            out_h.copy_(out_d, non_blocking=True)
+            one_step()
         for _ in range(warmup):
             g.replay()
         st.synchronize()
@@ -213,7 +242,7 @@ def stream_latency(op, dev, n_streams=4096, steps=10000, warmup=200):
     pick = lambda a, q: a[min(len(a) - 1, int(q * len(a)))]
     return {"workload": "C5: %d live streams, one 170-sample hop per stream per step, CUDA graph "
                         "(H2D hops + step kernel + D2H columns)" % n_streams,
-            "steps": steps, "device_us_p50": pick(dev_us, 0.5), "device_us_p99": pick(dev_us, 0.99),
+            "groups": groups, "zero_copy": zero_copy, "steps": steps, "device_us_p50": pick(dev_us, 0.5), "device_us_p99": pick(dev_us, 0.99),
             "host_us_p50": pick(wall_us, 0.5), "host_us_p99": pick(wall_us, 0.99),
             "realtime_budget_us": 170 / 16000 * 1e6,
             "frames_per_sec_at_p50": n_streams / (pick(wall_us, 0.5) * 1e-6)}
@@ -356,6 +385,9 @@ def main():
 
         for name, leg in (("fp32", leg_fp32), ("librosa_set", leg_librosa),
                           ("streaming", lambda: stream_latency(op, dev, 4096, args.stream_steps)),
+                          # same step, but the kernel writes the columns straight into pinned host memory
+                          ("streaming_hostwrite", lambda: stream_latency(op, dev, 4096, max(1000, args.stream_steps // 2),
+                                                                        zero_copy="out")),
                           ("streaming_fp32", leg_stream_fp32)):
             try:
                 extras[name] = leg()

@@ -151,6 +151,10 @@ int  mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_f
  * hold, preemph.py:18-21, frame.py:65-73).  Zero state = the core after reset with
  * nfft-hop zeros already pushed in.
  *   d_hop  [n_streams][hop] int16     d_out [n_streams][nceptrums]
+ * d_hop and d_out may be any pointers the device can dereference: device memory, or
+ * page-locked host memory under unified addressing (the kernel then moves those bytes over
+ * PCIe itself; writing d_out that way saves a copy operation per step, bench.py
+ * "streaming_hostwrite").  A group of streams is stepped by offsetting all three pointers.
  */
 int  mfcc_b200_state_bytes(void *handle, int32_t n_streams, int64_t *bytes);
 int  mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n_streams,

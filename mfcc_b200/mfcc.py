@@ -163,21 +163,46 @@ class MFCC:
             self._state.zero_()
         return self
 
-    def step(self, hop, out=None):
+    def step(self, hop, out=None, first_stream=None):
         """One hop (nfft//3 samples) per stream in, one cepstrum column per stream
         out: ``[S, hop]`` int16 -> ``[S, nceptrums]`` int16.  The state after reset()
-        is the core with nfft-hop zeros already pushed in."""
-        _check_samples(hop, self.device)
+        is the core with nfft-hop zeros already pushed in.
+
+        With ``first_stream`` the rows are the hops of streams ``first_stream ..
+        first_stream + S - 1`` of a state allocated by ``reset(n_streams)``: groups of
+        streams can then be stepped on different CUDA streams, so that the copy-in of
+        one group overlaps the kernel of another.
+
+        ``hop`` and ``out`` may also be PINNED host tensors: under unified addressing the
+        kernel then reads the hops and writes the columns over PCIe itself (zero-copy),
+        which removes the two copy operations from a latency-critical step."""
+        if isinstance(hop, torch.Tensor) and hop.device.type == "cpu":
+            if not hop.is_pinned() or hop.dtype != torch.int16:
+                raise ValueError("a host hop tensor must be pinned int16")
+            if out is not None and out.device.type == "cpu" and not out.is_pinned():
+                raise ValueError("a host out tensor must be pinned")
+        else:
+            _check_samples(hop, self.device)
         if hop.dim() != 2 or hop.shape[1] != self.cfg.hop:
             raise ValueError("hop must be [S, %d]" % self.cfg.hop)
         S = hop.shape[0]
-        if self._state is None or self._state.shape[0] != S:
-            self.reset(S)
-        hop = hop.contiguous()
+        if first_stream is None:
+            if self._state is None or self._state.shape[0] != S:
+                self.reset(S)
+            state = self._state
+        else:
+            if self._state is None or first_stream < 0 or first_stream + S > self._state.shape[0]:
+                raise ValueError("streams %d..%d are outside the state allocated by reset()"
+                                 % (first_stream, first_stream + S - 1))
+            state = self._state[first_stream:first_stream + S]
+        if not hop.is_contiguous():
+            hop = hop.contiguous()
         if out is None:
             out = torch.empty((S, self.nceptrums), dtype=self.out_dtype, device=self.device)
+        elif out.shape != (S, self.nceptrums) or out.dtype != self.out_dtype or not out.is_contiguous():
+            raise ValueError("out must be contiguous %s [%d, %d]" % (self.out_dtype, S, self.nceptrums))
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().mfcc_b200_step(
-                self._h.ptr, C.c_void_p(self._state.data_ptr()), C.c_void_p(hop.data_ptr()), S,
+                self._h.ptr, C.c_void_p(state.data_ptr()), C.c_void_p(hop.data_ptr()), S,
                 C.c_void_p(out.data_ptr()), _stream_ptr(self.device)))
         return out

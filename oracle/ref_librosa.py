@@ -66,11 +66,17 @@ def num_frames(n, hop=170):
     return 1 + n // hop
 
 
-def mfcc(x, sr=16000, hop=170, n_mfcc=32, n_fft=2048, n_mels=128, amin=1e-10, top_db=80.0, taps=False):
-    """x: int16 samples.  Returns float64 [frames][n_mfcc] (librosa returns the transpose)."""
+def mfcc(x, sr=16000, hop=170, n_mfcc=32, n_fft=2048, n_mels=128, amin=1e-10, top_db=80.0, taps=False,
+         center=True):
+    """x: int16 samples.  Returns float64 [frames][n_mfcc] (librosa returns the transpose).
+    center=False (librosa's stft option): frames start at t*hop, no padding."""
     y = np.asarray(x, dtype=np.float64) / 32768.0               # librosa.load of a 16-bit file
-    yp = np.pad(y, n_fft // 2, mode="reflect")
-    K = num_frames(len(y), hop)
+    if center:
+        yp = np.pad(y, n_fft // 2, mode="reflect")
+        K = num_frames(len(y), hop)
+    else:
+        yp = y
+        K = 1 + (len(y) - n_fft) // hop if len(y) >= n_fft else 0
     idx = hop * np.arange(K)[:, None] + np.arange(n_fft)[None, :]
     frames = yp[idx] * hann(n_fft)
     S = np.abs(np.fft.rfft(frames, axis=1)) ** 2

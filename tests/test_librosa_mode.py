@@ -115,6 +115,13 @@ def test_cuda_librosa_other_sizes_and_scale_chain(wav):
         ref = L.mfcc(x, hop=kw["hop_length"], n_mfcc=kw["n_mfcc"], n_mels=kw["n_mels"],
                      top_db=kw.get("top_db", 80.0) if kw.get("top_db", 80.0) is not None else 1e9)
         _close(op(xd).cpu().numpy(), ref)
+    # uncentred frames (stft center=False), another rate (different filter bank -> run-time step counts)
+    op = mfcc_b200.LibrosaMFCC(device="cuda:0", center=False, hop_length=256)
+    got = op(xd).cpu().numpy()
+    assert got.shape == (1 + (len(x) - 2048) // 256, 32)
+    _close(got, L.mfcc(x, hop=256, center=False))
+    op = mfcc_b200.LibrosaMFCC(sr=22050, device="cuda:0")
+    _close(op(xd).cpu().numpy(), L.mfcc(x, sr=22050))
     # genlibrosa.py:25-28: scale over time, then int16
     op = mfcc_b200.LibrosaMFCC(device="cuda:0")
     got = post.scale(op(xd)).cpu().numpy()
