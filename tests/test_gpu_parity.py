@@ -238,3 +238,34 @@ def test_all_kernels_driver():
     import runpy
     runpy.run_path(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
                                 "profiles", "all_kernels.py"), run_name="__main__")
+
+
+@pytest.mark.gpu
+def test_streaming_groups_and_pinned_host_buffers(ops):
+    """step(first_stream=...) on groups of streams and step() on pinned host tensors
+    (the kernel reads / writes them over PCIe itself) give the columns of a plain step."""
+    import torch
+    op = ops[(32, 32)]
+    S = 300
+    g = torch.Generator().manual_seed(4)
+    hops = [torch.randint(-32768, 32768, (S, 170), dtype=torch.int16, generator=g) for _ in range(4)]
+    op.reset(S)
+    want = [op.step(h.to("cuda:0")).cpu() for h in hops]
+    op.reset(S)
+    for h, w in zip(hops, want):
+        hd = h.to("cuda:0")
+        out = torch.empty((S, 32), dtype=torch.int16, device="cuda:0")
+        for a, b in ((0, 7), (7, 160), (160, S)):
+            op.step(hd[a:b], out=out[a:b], first_stream=a)
+        assert torch.equal(out.cpu(), w)
+    op.reset(S)
+    oh = torch.empty((S, 32), dtype=torch.int16).pin_memory()
+    for h, w in zip(hops, want):
+        op.step(h.pin_memory(), out=oh)
+        torch.cuda.synchronize()
+        assert torch.equal(oh, w)
+    with pytest.raises(ValueError):
+        op.step(hops[0][:10].to("cuda:0"), first_stream=S - 5)
+    with pytest.raises(ValueError):
+        op.step(hops[0])                                        # pageable host memory
+    op.reset(0)
