@@ -41,15 +41,16 @@ constexpr int LR_ROW = 33;                    // row pitch of the transposition 
 constexpr int LR_WBUF = 32 * LR_ROW;          // float2 per warp: transposition, spectrum, power
 constexpr int LR_MAX_MELS = 128;
 constexpr int LR_MAX_MFCC = 64;
-constexpr int LR_SLOTS = 4;                   // mel filters per lane
+constexpr int LR_SLOTS = 5;                   // mel segments per lane (129 segments for 128 filters)
+constexpr int LR_SCR_A = 1100, LR_SCR_B = 1260; // per-warp scratch (floats, inside the warp buffer) for the segment sums
 
 struct LrDev {                                 // device-resident tables of one handle
     float *window;                             // [2048], includes the 1/32768 input scale
     float2 *tw32x32;                           // [k1][lane] = exp(-2 pi i k1 lane / 1024)
     float2 *tw2048;                            // [513]  exp(-2 pi i k / 2048)
-    int *mel_id, *mel_base;                    // [4][32] filter of lane l in slot s (-1: none), its first bin
-    float *melT;                               // [steps][32] weight of each lane at each step
-    int mel_steps[LR_SLOTS];                   // steps of each slot (longest span in the slot)
+    int *mel_seg, *mel_base;                   // [5][32] segment of lane l in slot s (-1: none), its first bin
+    float2 *melT;                              // [steps][32] (rise, fall) weight of each lane at each step
+    int mel_steps[LR_SLOTS];                   // steps of each slot (longest segment in the slot)
     float *dct;                                // [n_mels][n_mfcc] (transposed for the lanes)
 };
 
@@ -126,17 +127,17 @@ __device__ __forceinline__ void fft32(float2 (&v)[32])
 }
 
 // Shared memory of lr_logmel (dynamic): [tw32x32 1024][tw2048 520] float2, then the mel
-// weight table [steps][32] float, then one LR_WBUF float2 buffer per warp.
+// weight table [steps][32] float2, then one LR_WBUF float2 buffer per warp.
 constexpr int LR_TW2048_PAD = 520;
 __host__ __device__ constexpr size_t lr_smem_bytes(int steps) {
-    return (size_t)(1024 + LR_TW2048_PAD) * sizeof(float2) + (size_t)steps * 32 * sizeof(float) +
+    return (size_t)(1024 + LR_TW2048_PAD) * sizeof(float2) + (size_t)steps * 32 * sizeof(float2) +
            (size_t)LR_WARPS * LR_WBUF * sizeof(float2);
 }
 
 // d_x [n_clips][clip_stride] int16; logmel [n_clips][n_frames][n_mels]; clipmax [n_clips] keys
-// FIXED: the mel step counts are the default bank's (6, 10, 22, 48: 128 Slaney filters at
-// 16 kHz), known at compile time and fully unrolled; otherwise they come from the tables.
-__host__ __device__ constexpr int lr_def_steps(int s) { return s == 0 ? 6 : s == 1 ? 10 : s == 2 ? 22 : 48; }
+// FIXED: the mel step counts are the default bank's (128 Slaney filters at 16 kHz), known at
+// compile time and fully unrolled; otherwise they come from the tables.
+__host__ __device__ constexpr int lr_def_steps(int s) { return s == 0 ? 3 : s == 1 ? 3 : s == 2 ? 5 : s == 3 ? 11 : 25; }
 template <bool FIXED>
 __global__ void __launch_bounds__(LR_THREADS, 2)
 lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_samples, int n_clips,
@@ -146,10 +147,10 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
     extern __shared__ __align__(16) unsigned char lr_smem_raw[];
     float2 *tw = reinterpret_cast<float2 *>(lr_smem_raw);              // [k1][lane]
     float2 *tw2 = tw + 1024;                                           // exp(-2 pi i k / 2048)
-    float *wT = reinterpret_cast<float *>(tw2 + LR_TW2048_PAD);        // [step][lane]
-    const int steps = t.mel_steps[0] + t.mel_steps[1] + t.mel_steps[2] + t.mel_steps[3];
+    float2 *wT = tw2 + LR_TW2048_PAD;                                  // [step][lane] (rise, fall)
+    const int steps = t.mel_steps[0] + t.mel_steps[1] + t.mel_steps[2] + t.mel_steps[3] + t.mel_steps[4];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    float2 *buf = reinterpret_cast<float2 *>(wT + steps * 32) + warp * LR_WBUF;
+    float2 *buf = wT + steps * 32 + warp * LR_WBUF;
     float *pw = reinterpret_cast<float *>(buf);                        // [1025] after the split
 
     for (int i = tid; i < 1024; i += LR_THREADS) tw[i] = t.tw32x32[i];
@@ -159,11 +160,11 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
     for (int i = lane; i < LR_WBUF; i += 32) buf[i] = make_float2(0.0f, 0.0f);
     __syncthreads();
 
-    // frame-invariant per-lane values: the four mel filters of this lane
-    int mid[LR_SLOTS], mlo[LR_SLOTS];
+    // frame-invariant per-lane values: the mel segments this lane walks
+    int mseg[LR_SLOTS], mlo[LR_SLOTS];
 #pragma unroll
     for (int s = 0; s < LR_SLOTS; s++) {
-        mid[s] = __ldg(t.mel_id + 32 * s + lane);
+        mseg[s] = __ldg(t.mel_seg + 32 * s + lane);
         mlo[s] = __ldg(t.mel_base + 32 * s + lane);
     }
     const float2 *win2 = reinterpret_cast<const float2 *>(t.window) + lane;
@@ -260,34 +261,51 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
             for (int k = lane; k < LR_BINS; k += 32) dst[k] = pw[k];
         }
 
-        // mel filters: lane l owns filters l, 63-l, 64+l, 127-l (narrow ones pair with wide
-        // ones); weights sit in shared memory as [step][lane], zero beyond a filter's span
-        float db = -3.0e38f;
-        float *lm = logmel + item * n_mels;
-        const float *w = wT + lane;
+        // Mel filters by segments, the way the reference's FilterBank does it
+        // (mfcc/core/filterbank.py:119-134): the bins between two filter centres feed the
+        // rising side of one filter and the falling side of the previous one, so one pass
+        // over a segment with a (rise, fall) weight pair per bin yields both partial sums and
+        // every power value is read once.  Lane l walks one segment per slot; weights sit in
+        // shared memory as [step][lane], zero beyond a segment's end.
+        const float2 *w = wT + lane;
 #pragma unroll
         for (int s = 0; s < LR_SLOTS; s++) {
             const int n = FIXED ? lr_def_steps(s) : t.mel_steps[s];
             const float *p = pw + mlo[s];
-            float a0 = 0.0f, a1 = 0.0f;
+            float ra = 0.0f, fa = 0.0f;
             if (FIXED) {
 #pragma unroll
-                for (int i = 0; i < lr_def_steps(s); i += 2) {
-                    a0 = fmaf(w[i * 32], p[i], a0);
-                    a1 = fmaf(w[i * 32 + 32], p[i + 1], a1);       // every default count is even
+                for (int i = 0; i < lr_def_steps(s); i++) {
+                    const float2 ww = w[i * 32];
+                    const float d = p[i];
+                    ra = fmaf(ww.x, d, ra);
+                    fa = fmaf(ww.y, d, fa);
                 }
             } else {
-                int i = 0;
-                for (; i + 1 < n; i += 2) {
-                    a0 = fmaf(w[i * 32], p[i], a0);
-                    a1 = fmaf(w[i * 32 + 32], p[i + 1], a1);
+#pragma unroll 2
+                for (int i = 0; i < n; i++) {
+                    const float2 ww = w[i * 32];
+                    const float d = p[i];
+                    ra = fmaf(ww.x, d, ra);
+                    fa = fmaf(ww.y, d, fa);
                 }
-                if (i < n) a0 = fmaf(w[i * 32], p[i], a0);
             }
             w += n * 32;
-            if (mid[s] >= 0) {
-                const float d = 3.0102999566398120f * __log2f(fmaxf(a0 + a1, amin));     // 10 log10
-                lm[mid[s]] = d;
+            if (mseg[s] >= 0) {
+                pw[LR_SCR_A + mseg[s]] = ra;
+                pw[LR_SCR_B + mseg[s]] = fa;
+            }
+        }
+        __syncwarp();
+        float db = -3.0e38f;
+        float *lm = logmel + item * n_mels;
+#pragma unroll
+        for (int j = 0; j < LR_MAX_MELS / 32; j++) {
+            const int m = lane + 32 * j;                        // filter m = rise of segment m + fall of segment m + 1
+            if (m < n_mels) {
+                const float e = pw[LR_SCR_A + m] + pw[LR_SCR_B + m + 1];
+                const float d = 3.0102999566398120f * __log2f(fmaxf(e, amin));           // 10 log10
+                lm[m] = d;
                 db = fmaxf(db, d);
             }
         }
@@ -407,38 +425,69 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
             tw1[k1 * 32 + L] = make_float2((float)cos(ang), (float)-sin(ang));
         }
     for (int k = 0; k < 513; k++) tw2[k] = make_float2((float)cos(2 * PI * k / 2048), (float)-sin(2 * PI * k / 2048));
-    // lane l owns filters l, 63-l, 64+l, 127-l (slots 0..3): narrow low filters pair with wide
-    // high ones; every slot runs as many steps as its widest filter
-    std::vector<int> lo(cfg->n_mels), cnt(cfg->n_mels), ids(LR_SLOTS * 32, -1), base(LR_SLOTS * 32, 0);
-    for (int m = 0; m < cfg->n_mels; m++) {
-        const float *row = cfg->mel + (size_t)m * LR_BINS;
-        int a = 0, b = LR_BINS;
-        while (a < LR_BINS && row[a] == 0.0f) a++;
-        while (b > a && row[b - 1] == 0.0f) b--;
-        lo[m] = a < LR_BINS ? a : 0;
-        cnt[m] = b - a;
+    // Segments: every bin may feed two consecutive filters.  Segment g holds the bins whose
+    // filters are {g-1, g}; its bins carry the rise weight of filter g and the fall weight
+    // of filter g-1 (the structure of any bank of ordered, half-overlapping triangles).
+    const int nm = cfg->n_mels, nseg = nm + 1;
+    std::vector<int> seg(LR_BINS), first(nseg, -1), len(nseg, 0);
+    {
+        int cur = 0;
+        for (int b = 0; b < LR_BINS; b++) {
+            int lo = -1, hi = -1;
+            for (int m = 0; m < nm; m++)
+                if (cfg->mel[(size_t)m * LR_BINS + b] != 0.0f) { if (lo < 0) lo = m; hi = m; }
+            int g = cur;
+            if (lo >= 0) {
+                if (hi - lo > 1) { delete h; return fail_ext(MFCC_B200_EUNSUPPORTED, "mel: a bin feeds more than two consecutive filters"); }
+                if (hi > lo) g = hi;
+                else {
+                    // one filter only: on its falling side (weight going down, or already in the
+                    // next segment) the bin belongs to segment lo+1, else to segment lo
+                    const bool falling = b > 0 && cfg->mel[(size_t)lo * LR_BINS + b] < cfg->mel[(size_t)lo * LR_BINS + b - 1];
+                    g = (falling || cur == lo + 1) ? lo + 1 : (cur > lo ? cur : lo);
+                }
+                if (g < cur || g > lo + 1 || g > nm) { delete h; return fail_ext(MFCC_B200_EUNSUPPORTED, "mel: filters are not ordered triangles"); }
+            }
+            seg[b] = cur = g;
+        }
+        for (int b = 0; b < LR_BINS; b++) { if (first[seg[b]] < 0) first[seg[b]] = b; ++len[seg[b]]; }
+        // every non-zero weight must be accounted for by the (rise, fall) pair of its bin
+        for (int m = 0; m < nm; m++)
+            for (int b = 0; b < LR_BINS; b++)
+                if (cfg->mel[(size_t)m * LR_BINS + b] != 0.0f && seg[b] != m && seg[b] != m + 1) {
+                    delete h;
+                    return fail_ext(MFCC_B200_EUNSUPPORTED, "mel: filters are not ordered triangles");
+                }
     }
+    // lane l walks one segment per slot; the first slot takes what is left over after full
+    // blocks of 32 (the shortest segments), every slot runs as many steps as its longest segment
+    const int nslots = (nseg + 31) / 32, head = nseg - 32 * (nslots - 1);
+    std::vector<int> segs(LR_SLOTS * 32, -1), base(LR_SLOTS * 32, 0);
     int steps = 0, soff[LR_SLOTS];
     for (int s = 0; s < LR_SLOTS; s++) {
         int n = 0;
-        for (int l = 0; l < 32; l++) {
-            const int m = s == 0 ? l : s == 1 ? 63 - l : s == 2 ? 64 + l : 127 - l;
-            if (m >= cfg->n_mels) continue;
-            ids[32 * s + l] = m;
-            base[32 * s + l] = lo[m];
-            n = std::max(n, cnt[m]);
+        for (int l = 0; l < 32 && s < nslots; l++) {
+            const int g = s == 0 ? (l < head ? l : -1) : head + 32 * (s - 1) + l;
+            if (g < 0 || g >= nseg) continue;
+            segs[32 * s + l] = g;
+            base[32 * s + l] = first[g] < 0 ? 0 : first[g];
+            n = std::max(n, len[g]);
         }
         h->dev.mel_steps[s] = n;
         soff[s] = steps;
         steps += n;
     }
-    std::vector<float> wT((size_t)std::max(1, steps) * 32, 0.0f);
+    std::vector<float2> wT((size_t)std::max(1, steps) * 32, make_float2(0.0f, 0.0f));
     for (int s = 0; s < LR_SLOTS; s++)
         for (int l = 0; l < 32; l++) {
-            const int m = ids[32 * s + l];
-            if (m < 0) continue;
-            const float *row = cfg->mel + (size_t)m * LR_BINS;
-            for (int i = 0; i < cnt[m]; i++) wT[(size_t)(soff[s] + i) * 32 + l] = row[lo[m] + i];
+            const int g = segs[32 * s + l];
+            if (g < 0) continue;
+            for (int i = 0; i < len[g]; i++) {
+                const int b = first[g] + i;
+                const float rise = g < nm ? cfg->mel[(size_t)g * LR_BINS + b] : 0.0f;
+                const float fall = g >= 1 ? cfg->mel[(size_t)(g - 1) * LR_BINS + b] : 0.0f;
+                wT[(size_t)(soff[s] + i) * 32 + l] = make_float2(rise, fall);
+            }
         }
     h->smem1 = lr_smem_bytes(steps);
     std::vector<float> dT((size_t)cfg->n_mels * cfg->n_mfcc);
@@ -458,9 +507,9 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
     h->dev.window = (float *)upload(cfg->window, LR_NFFT * sizeof(float));
     h->dev.tw32x32 = (float2 *)upload(tw1.data(), tw1.size() * sizeof(float2));
     h->dev.tw2048 = (float2 *)upload(tw2.data(), tw2.size() * sizeof(float2));
-    h->dev.mel_id = (int *)upload(ids.data(), ids.size() * sizeof(int));
+    h->dev.mel_seg = (int *)upload(segs.data(), segs.size() * sizeof(int));
     h->dev.mel_base = (int *)upload(base.data(), base.size() * sizeof(int));
-    h->dev.melT = (float *)upload(wT.data(), wT.size() * sizeof(float));
+    h->dev.melT = (float2 *)upload(wT.data(), wT.size() * sizeof(float2));
     if (e == cudaSuccess && h->smem1 > 200 * 1024) {
         for (void *p : h->allocs) cudaFree(p);
         delete h;
