@@ -42,13 +42,14 @@ constexpr int LR_WBUF = 32 * LR_ROW;          // float2 per warp: transposition,
 constexpr int LR_MAX_MELS = 128;
 constexpr int LR_MAX_MFCC = 64;
 constexpr int LR_SLOTS = 5;                   // mel segments per lane (129 segments for 128 filters)
-constexpr int LR_SCR_A = 1100, LR_SCR_B = 1260; // per-warp scratch (floats, inside the warp buffer) for the segment sums
+constexpr int LR_SCR_A = 1400, LR_SCR_B = 1568; // per-warp scratch (floats, inside the warp buffer) for the segment sums
 
 struct LrDev {                                 // device-resident tables of one handle
     float *window;                             // [2048], includes the 1/32768 input scale
     float2 *tw32x32;                           // [k1][lane] = exp(-2 pi i k1 lane / 1024)
     float2 *tw2048;                            // [513]  exp(-2 pi i k / 2048)
-    int *mel_seg, *mel_base;                   // [5][32] segment of lane l in slot s (-1: none), its first bin
+    int *mel_seg, *mel_base;                   // [5][32] segment of lane l in slot s (-1: none), padded address of its first bin
+    uint16_t *paddr;                           // [1025 (+pad)] bin -> word of the bank-padded power layout
     float2 *melT;                              // [steps][32] (rise, fall) weight of each lane at each step
     int mel_steps[LR_SLOTS];                   // steps of each slot (longest segment in the slot)
     float *dct;                                // [n_mels][n_mfcc] (transposed for the lanes)
@@ -126,11 +127,14 @@ __device__ __forceinline__ void fft32(float2 (&v)[32])
     }
 }
 
-// Shared memory of lr_logmel (dynamic): [tw32x32 1024][tw2048 520] float2, then the mel
-// weight table [steps][32] float2, then one LR_WBUF float2 buffer per warp.
+// Shared memory of lr_logmel (dynamic): [tw32x32 1024][tw2048 520] float2, the bin -> padded
+// address table (1032 uint16), then the mel weight table [steps][32] float2, then one
+// LR_WBUF float2 buffer per warp.
 constexpr int LR_TW2048_PAD = 520;
+constexpr int LR_PADDR_PAD = 1032;            // uint16 entries, a multiple of 4 (keeps float2 alignment)
 __host__ __device__ constexpr size_t lr_smem_bytes(int steps) {
-    return (size_t)(1024 + LR_TW2048_PAD) * sizeof(float2) + (size_t)steps * 32 * sizeof(float2) +
+    return (size_t)(1024 + LR_TW2048_PAD) * sizeof(float2) + LR_PADDR_PAD * sizeof(uint16_t) +
+           (size_t)steps * 32 * sizeof(float2) +
            (size_t)LR_WARPS * LR_WBUF * sizeof(float2);
 }
 
@@ -147,7 +151,8 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
     extern __shared__ __align__(16) unsigned char lr_smem_raw[];
     float2 *tw = reinterpret_cast<float2 *>(lr_smem_raw);              // [k1][lane]
     float2 *tw2 = tw + 1024;                                           // exp(-2 pi i k / 2048)
-    float2 *wT = tw2 + LR_TW2048_PAD;                                  // [step][lane] (rise, fall)
+    uint16_t *pa = reinterpret_cast<uint16_t *>(tw2 + LR_TW2048_PAD);  // bin -> padded power address
+    float2 *wT = reinterpret_cast<float2 *>(pa + LR_PADDR_PAD);        // [step][lane] (rise, fall)
     const int steps = t.mel_steps[0] + t.mel_steps[1] + t.mel_steps[2] + t.mel_steps[3] + t.mel_steps[4];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float2 *buf = wT + steps * 32 + warp * LR_WBUF;
@@ -155,6 +160,7 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
 
     for (int i = tid; i < 1024; i += LR_THREADS) tw[i] = t.tw32x32[i];
     for (int i = tid; i < 513; i += LR_THREADS) tw2[i] = t.tw2048[i];
+    for (int i = tid; i < LR_BINS; i += LR_THREADS) pa[i] = t.paddr[i];
     for (int i = tid; i < steps * 32; i += LR_THREADS) wT[i] = t.melT[i];
     // the mel walk reads a few zero-weighted words past bin 1024: they must be finite
     for (int i = lane; i < LR_WBUF; i += 32) buf[i] = make_float2(0.0f, 0.0f);
@@ -251,14 +257,14 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
             const float2 G = make_float2(0.5f * (za.y + zb.y), -0.5f * (za.x - zb.x));
             const float2 T = cmul(G, tw2[k]);
             const float pr = F.x + T.x, pi = F.y + T.y, qr = F.x - T.x, qi = F.y - T.y;
-            pw[k] = pr * pr + pi * pi;
-            pw[LR_HALF - k] = qr * qr + qi * qi;
+            pw[pa[k]] = pr * pr + pi * pi;                      // bank-padded layout: see the mel walk
+            pw[pa[LR_HALF - k]] = qr * qr + qi * qi;
         }
-        if (lane == 0) pw[512] = zc.x * zc.x + zc.y * zc.y;     // W^512 = -i
+        if (lane == 0) pw[pa[512]] = zc.x * zc.x + zc.y * zc.y;     // W^512 = -i
         __syncwarp();
         if (power_tap) {
             float *dst = power_tap + item * LR_BINS;
-            for (int k = lane; k < LR_BINS; k += 32) dst[k] = pw[k];
+            for (int k = lane; k < LR_BINS; k += 32) dst[k] = pw[pa[k]];
         }
 
         // Mel filters by segments, the way the reference's FilterBank does it
@@ -266,7 +272,9 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
         // rising side of one filter and the falling side of the previous one, so one pass
         // over a segment with a (rise, fall) weight pair per bin yields both partial sums and
         // every power value is read once.  Lane l walks one segment per slot; weights sit in
-        // shared memory as [step][lane], zero beyond a segment's end.
+        // shared memory as [step][lane], zero beyond a segment's end.  Segments are disjoint,
+        // so the power values are laid out with gaps that start every segment of a slot in a
+        // bank of its own: the 32 lanes' walks never collide.
         const float2 *w = wT + lane;
 #pragma unroll
         for (int s = 0; s < LR_SLOTS; s++) {
@@ -462,7 +470,20 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
     // lane l walks one segment per slot; the first slot takes what is left over after full
     // blocks of 32 (the shortest segments), every slot runs as many steps as its longest segment
     const int nslots = (nseg + 31) / 32, head = nseg - 32 * (nslots - 1);
-    std::vector<int> segs(LR_SLOTS * 32, -1), base(LR_SLOTS * 32, 0);
+    std::vector<int> segs(LR_SLOTS * 32, -1), base(LR_SLOTS * 32, 0), pbase(nseg, 0);
+    {
+        // padded layout: the segments of one slot start in 32 different banks
+        bool used[LR_SLOTS][32] = {};
+        int next = 0;
+        for (int g = 0; g < nseg; g++) {
+            const int s = g < head ? 0 : 1 + (g - head) / 32;
+            int a = next;
+            while (used[s][a & 31]) a++;
+            used[s][a & 31] = true;
+            pbase[g] = a;
+            next = a + len[g];
+        }
+    }
     int steps = 0, soff[LR_SLOTS];
     for (int s = 0; s < LR_SLOTS; s++) {
         int n = 0;
@@ -470,12 +491,22 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
             const int g = s == 0 ? (l < head ? l : -1) : head + 32 * (s - 1) + l;
             if (g < 0 || g >= nseg) continue;
             segs[32 * s + l] = g;
-            base[32 * s + l] = first[g] < 0 ? 0 : first[g];
+            base[32 * s + l] = pbase[g];
             n = std::max(n, len[g]);
         }
         h->dev.mel_steps[s] = n;
         soff[s] = steps;
         steps += n;
+    }
+    std::vector<uint16_t> paddr(LR_PADDR_PAD, 0);
+    int max_read = 0;
+    for (int b = 0; b < LR_BINS; b++) paddr[b] = (uint16_t)(pbase[seg[b]] + (b - first[seg[b]]));
+    for (int s = 0; s < LR_SLOTS; s++)
+        for (int l = 0; l < 32; l++)
+            if (segs[32 * s + l] >= 0) max_read = std::max(max_read, base[32 * s + l] + h->dev.mel_steps[s]);
+    if (max_read > LR_SCR_A || LR_SCR_B + nseg > 2 * LR_WBUF) {
+        delete h;
+        return fail_ext(MFCC_B200_EUNSUPPORTED, "mel: padded power layout does not fit the warp buffer");
     }
     std::vector<float2> wT((size_t)std::max(1, steps) * 32, make_float2(0.0f, 0.0f));
     for (int s = 0; s < LR_SLOTS; s++)
@@ -509,6 +540,7 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
     h->dev.tw2048 = (float2 *)upload(tw2.data(), tw2.size() * sizeof(float2));
     h->dev.mel_seg = (int *)upload(segs.data(), segs.size() * sizeof(int));
     h->dev.mel_base = (int *)upload(base.data(), base.size() * sizeof(int));
+    h->dev.paddr = (uint16_t *)upload(paddr.data(), paddr.size() * sizeof(uint16_t));
     h->dev.melT = (float2 *)upload(wT.data(), wT.size() * sizeof(float2));
     if (e == cudaSuccess && h->smem1 > 200 * 1024) {
         for (void *p : h->allocs) cudaFree(p);

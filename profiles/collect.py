@@ -46,6 +46,9 @@ def main():
         with open(os.path.join(P, "%s_%s_lines.txt" % (tag, k)), "w") as f:
             f.write(subprocess.run([sys.executable, os.path.join(P, "ncu_lines.py"), rep, str(FRAMES), "60"],
                                    capture_output=True, text=True).stdout)
+        with open(os.path.join(P, "%s_%s_wavefronts.txt" % (tag, k)), "w") as f:
+            f.write(subprocess.run([sys.executable, os.path.join(P, "ncu_wavefronts.py"), rep, str(FRAMES), "30"],
+                                   capture_output=True, text=True).stdout)
         d, u = raw(rep)
         issue[name] = {
             "warp_inst_per_frame": float(d["smsp__inst_executed.sum"].replace(",", "")) / FRAMES,
