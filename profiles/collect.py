@@ -30,7 +30,7 @@ def main():
     global FRAMES
     tag = sys.argv[1]
     for suffix in ("bench_full.json", "bench_reference.json", "launches.csv", "pipe_bench.jsonl", "pytest.txt",
-                   "librosa_rate.txt"):
+                   "librosa_rate.txt", "accuracy.txt"):
         src = os.path.join(G, "%s_%s" % (tag, suffix))
         if os.path.exists(src):
             shutil.copy(src, os.path.join(P, "%s_%s" % (tag, suffix)))

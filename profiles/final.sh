@@ -17,4 +17,5 @@ ncu --set full --import-source on --clock-control none -k regex:mfcc_int_fused -
 ncu --set full --import-source on --clock-control none -k regex:mfcc_f32_fused -s 2 -c 1 -f -o $o/${tag}_f32 python profiles/run_both.py 300 > /dev/null 2>&1
 ncu --set full --import-source on --clock-control none -k regex:lr_logmel -s 3 -c 1 -f -o $o/${tag}_lr python profiles/run_librosa.py 300 > /dev/null 2>&1
 python profiles/run_librosa.py 300 > $o/${tag}_librosa_rate.txt 2>/dev/null
+python profiles/accuracy.py > $o/${tag}_accuracy.txt 2>/dev/null
 ls -la $o | tail -12
