@@ -176,3 +176,56 @@ def test_gpu_converter_writes_the_reference_tools_files(tmp_path, wav):
         a = open(os.path.join(ref_root, rel)[:-3] + "mfcc", "rb").read()
         b = open(os.path.join(gpu_root, rel)[:-3] + "mfcc", "rb").read()
         assert a == b and len(a) > 0, rel
+
+
+# ---------------------------------------------------------------- the C host tool over the C ABI
+def _build_c_tool():
+    import subprocess
+    host = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "host")
+    subprocess.check_call(["make", "-C", host, "-s"])
+    return os.path.join(host, "wav2mfcc")
+
+
+def test_c_host_tool_builds_and_fails_loudly_without_a_gpu(tmp_path):
+    """host/wav2mfcc.c: the reference's tool in its own language on top of include/mfcc_b200.h.
+    It must link against the library with nothing but the header, print the reference's
+    usage line, and report the CUDA error instead of producing files when there is no GPU."""
+    import subprocess
+    import torch
+    exe = _build_c_tool()
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 1 and r.stdout.startswith("Usage:") and "<wavdir>" in r.stdout   # main.c:250-253
+    if not torch.cuda.is_available():
+        write_wav(str(tmp_path / "a.wav"), np.zeros(1000, dtype=np.int16))
+        r = subprocess.run([exe, str(tmp_path)], capture_output=True, text=True)
+        assert r.returncode == 2 and "mfcc_b200_create" in r.stdout
+        assert not os.path.exists(str(tmp_path / "a.mfcc"))
+
+
+@needs_ref_tool
+@pytest.mark.gpu
+def test_c_host_tool_writes_the_reference_tools_files(tmp_path, wav):
+    """Same directory through the reference's software/main.c (oracle-backed FPGA model) and
+    through host/wav2mfcc (plain C over the C ABI, GPU): byte-identical .mfcc files; files
+    the reference rejects are rejected with its messages."""
+    import subprocess
+    exe = _build_c_tool()
+    ref_root, c_root = str(tmp_path / "ref"), str(tmp_path / "c")
+    clips, _model, _cfg = _run_reference_tool(ref_root, wav)
+    clips = dict(clips)
+    for rel, x in clips.items():
+        os.makedirs(os.path.dirname(os.path.join(c_root, rel)), exist_ok=True)
+        write_wav(os.path.join(c_root, rel), x)
+    write_wav(os.path.join(c_root, "t", "rate.wav"), wav[:1000], rate=8000)
+    write_wav(os.path.join(c_root, "t", "stereo.wav"), wav[:1000], channels=2)
+    write_wav(os.path.join(c_root, "empty.wav"), np.zeros(0, dtype=np.int16))
+    r = subprocess.run([exe, c_root], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Unexpected samplerate: 8000" in r.stdout and "Unexpected channel count: 2" in r.stdout
+    assert "%d files converted, 2 rejected" % (len(clips) + 1) in r.stdout
+    for rel in clips:
+        a = open(os.path.join(ref_root, rel)[:-3] + "mfcc", "rb").read()
+        b = open(os.path.join(c_root, rel)[:-3] + "mfcc", "rb").read()
+        assert a == b and len(a) > 0, rel
+    assert os.path.getsize(os.path.join(c_root, "empty.mfcc")) == 64          # one zero-filled round
+    assert not os.path.exists(os.path.join(c_root, "t", "rate.mfcc"))
