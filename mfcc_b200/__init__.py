@@ -14,6 +14,9 @@ def __getattr__(name):
     if name == "MFCC":
         from .mfcc import MFCC
         return MFCC
+    if name == "LiveSession":
+        from .live import LiveSession
+        return LiveSession
     if name == "LibrosaMFCC":
         from .librosa_mode import LibrosaMFCC
         return LibrosaMFCC

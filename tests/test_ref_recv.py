@@ -73,3 +73,41 @@ def test_cuda_framing_and_gate_against_reference_receiver():
             assert bool(a[0]) == rx.active(), t
     finally:
         rx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("capture", [False, True])
+def test_live_session_against_reference_receiver(wav, capture):
+    """mfcc_b200.LiveSession = the mic build end to end (MFCC step + framing + gate) for
+    several streams; stream 0's serial bytes go into the reference's own receiver, whose
+    columns and gate decisions must match, and the columns must equal the batch path."""
+    import torch
+    import mfcc_b200
+    S, nc, nf, steps = 3, 16, 93, 200
+    loud = np.clip(wav[20000:20000 + 170 * steps].astype(np.int32) * 3, -32768, 32767).astype(np.int16)
+    x = np.stack([loud, wav[60000:60000 + 170 * steps], np.zeros(170 * steps, dtype=np.int16)])
+    ses = mfcc_b200.LiveSession(S, nceptrums=nc, device="cuda:0", capture=capture)
+    cols, wire, act = [], [], []
+    for t in range(steps):
+        c, w, _p, a = ses.push(torch.from_numpy(np.ascontiguousarray(x[:, 170 * t:170 * (t + 1)])).to("cuda:0"))
+        torch.cuda.synchronize()
+        cols.append(c.cpu().numpy().copy()); wire.append(w.cpu().numpy().copy()); act.append(a.cpu().numpy().copy())
+    cols = np.stack(cols, axis=1)                                # [S, steps, nc]
+    # the streaming state after reset holds 342 zeros: same columns as the batch path on that stream
+    op = mfcc_b200.MFCC(nfilters=32, nceptrums=nc, device="cuda:0")
+    xb = np.concatenate([np.zeros((S, 342), dtype=np.int16), x], axis=1)
+    want = op(torch.from_numpy(xb).to("cuda:0")).cpu().numpy()
+    assert np.array_equal(cols, want[:, :steps])
+    rx = RR.Receiver(nc, nf)
+    try:
+        assert rx.push(b"".join(wire[t][0].tobytes() for t in range(nf))) == nf
+        assert np.array_equal(rx.store.reshape(nf, nc), cols[0, :nf])
+        seen = set()
+        for t in range(nf, steps):
+            assert rx.push(wire[t][0].tobytes()) == 1
+            assert bool(act[t][0]) == rx.active(), t
+            seen.add(bool(act[t][0]))
+        assert True in seen                                      # the loud stream trips the gate
+    finally:
+        rx.close()
+    assert not np.stack(act)[:, 2].any()                         # the silent stream never does
