@@ -145,6 +145,13 @@ int  mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_f
                      int32_t stepsize, int32_t nfft, void *stream);
 
 /*
+ * PowerSpectrum(width=16, width_output) with any output width (mfcc/core/pow2.py:43-50; the
+ * class default and the reference's own bench use 24, pow2.py:44, :74; MFCC uses 30):
+ * d_out[i] = ((re*re + im*im) mod 2^32) >> (32 - width_output) for n_bins (re, im) pairs.
+ */
+int  mfcc_b200_power(const int16_t *d_in, uint32_t *d_out, int64_t n_bins, int32_t width_output, void *stream);
+
+/*
  * Streaming: one hop per stream per call, the mic2mfcc use of the core
  * (mfcc/targets/mic2mfcc.py:19-30).  d_state holds, per stream, the last nfft-hop
  * raw samples and the sample before them (what Preemph.odata and the Frame ring

@@ -129,6 +129,15 @@ __global__ void k_frame_general(const int16_t *y, int16_t *fr, long long n, long
     }
 }
 
+// PowerSpectrum(width=16, width_output), mfcc/core/pow2.py:32, :64: the 32-bit sum of the two
+// squares (it wraps for re = im = -32768), top width_output bits
+__global__ void k_power_general(const int16_t *f, uint32_t *pw, long long total, int shift) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int re = f[2 * i], im = f[2 * i + 1];
+        pw[i] = ((unsigned)(re * re) + (unsigned)(im * im)) >> shift;
+    }
+}
+
 inline int grid_for(long long total, int block) {
     long long g = (total + block - 1) / block;
     if (g > 148 * 16) g = 148 * 16;
@@ -166,6 +175,16 @@ int mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_fr
     if (!d_out || (n > 0 && !d_in)) return fail_ext(MFCC_B200_EINVAL, "null buffer");
     k_frame_general<<<grid_for(n_frames * nfft, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n, n_frames, windowlen,
                                                                                     stepsize, nfft);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_power(const int16_t *d_in, uint32_t *d_out, int64_t n_bins, int32_t width_output, void *stream)
+{
+    if (n_bins < 0 || width_output < 1 || width_output > 32) return fail_ext(MFCC_B200_EINVAL, "need n_bins >= 0 and 1 <= width_output <= 32");
+    if (n_bins == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_power_general<<<grid_for(n_bins, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n_bins, 32 - width_output);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
 }

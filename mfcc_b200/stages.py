@@ -139,20 +139,30 @@ class FftStream(_Stage):
 
 
 class PowerSpectrum(_Stage):
-    """PowerSpectrum(width=16, width_output=24), mfcc/core/pow2.py:43-50.
-    int16 [K, 256, 2] -> int32 [K, 256] (30-bit unsigned values)."""
+    """PowerSpectrum(width=16, width_output=24), mfcc/core/pow2.py:43-50, any output width:
+    int16 [..., 2] (re, im) -> int32 [...] holding the unsigned top ``width_output`` bits of
+    the 32-bit sum of squares (MFCC uses 30, mfcc.py:60-62)."""
     stage_id = _lib.STAGE_POWER
 
     def __init__(self, width=16, width_output=24, multiplier_cls=None, _handle=None, device=None):
-        if (width, width_output) != (16, 30):
-            raise ValueError("CUDA path covers PowerSpectrum(16, 30) (mfcc.py:60-62)")
+        if width != 16:
+            raise ValueError("width must be 16")
+        if not 1 <= width_output <= 32:
+            raise ValueError("width_output must be 1..32")
         self.width, self.width_output = width, width_output
-        self._setup(_handle, device)
+        if not torch.cuda.is_available():
+            raise RuntimeError("stage operators need a CUDA device: there is no CPU fallback")
+        self.device = torch.device(device if device is not None else
+                                   "cuda:%d" % torch.cuda.current_device())
 
     def __call__(self, spec):
-        x = self._check(spec, torch.int16, (256, 2))
+        x = self._check(spec, torch.int16, (2,))
         out = torch.empty(x.shape[:-1], dtype=torch.int32, device=self.device)
-        return self._run(x, out, x.numel() // 512)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_power(
+                C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), out.numel(), self.width_output,
+                C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class FilterBank(_Stage):

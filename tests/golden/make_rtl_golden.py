@@ -287,7 +287,8 @@ def frame_vectors():
     rng = np.random.default_rng(11)
     out = {}
     for name, (wl, st, nfft, nfr) in {"400_160_512": (400, 160, 512, 6), "512_170_512": (512, 170, 512, 4),
-                                      "96_96_128": (96, 96, 128, 5), "100_30_128": (100, 30, 128, 9)}.items():
+                                      "96_96_128": (96, 96, 128, 5), "100_30_128": (100, 30, 128, 9),
+                                      "25_8_32": (25, 8, 32, 12)}.items():      # frame.py:158, the reference's own bench
         n = wl + st * (nfr - 1) + 7
         x = rng.integers(-32768, 32768, n)
         dut = Frame(16, wl, st, nfft)
@@ -342,6 +343,36 @@ def frame_vectors():
     sim.run()
     out["preemph_in"] = x
     out["preemph_out"] = np.array(got, dtype=np.int64)
+
+    # PowerSpectrum(width=16) with the class default width_output = 24 (pow2.py:44, the bench at :74)
+    with contextlib.redirect_stdout(io.StringIO()):
+        from mfcc.core.pow2 import PowerSpectrum
+        from mfcc.misc.mul import Multiplier
+    pr = rng.integers(-32768, 32768, (48, 2))
+    pr[:4] = [[-32768, -32768], [32767, 32767], [-32768, 32767], [0, -1]]
+    dutp = PowerSpectrum(width=16, width_output=24, multiplier_cls=Multiplier)
+    simp = Simulator(dutp)
+    gotp = []
+
+    def powbench():
+        idx = 0
+        yield dutp.source.ready.eq(1)
+        while len(gotp) < len(pr):
+            yield dutp.sink.valid.eq(int(idx < len(pr)))
+            if idx < len(pr):
+                yield dutp.sink.data_r.eq(int(pr[idx, 0]))
+                yield dutp.sink.data_i.eq(int(pr[idx, 1]))
+            took = (yield dutp.sink.valid) and (yield dutp.sink.ready)
+            if (yield dutp.source.valid) and (yield dutp.source.ready):
+                gotp.append((yield dutp.source.data))
+            yield
+            if took:
+                idx += 1
+    simp.add_clock(1e-6)
+    simp.add_sync_process(powbench)
+    simp.run()
+    out["power24_in"] = pr
+    out["power24_out"] = np.array(gotp, dtype=np.int64)
     return out
 
 

@@ -189,7 +189,7 @@ def test_cuda_stage_operators_match_rtl_stage_vectors(sv):
 
 # ---------------------------------------------------------------- Frame / Preemph on their own
 FRAME_SETS = {"400_160_512": (400, 160, 512), "512_170_512": (512, 170, 512),
-              "96_96_128": (96, 96, 128), "100_30_128": (100, 30, 128)}
+              "96_96_128": (96, 96, 128), "100_30_128": (100, 30, 128), "25_8_32": (25, 8, 32)}
 
 
 @pytest.fixture(scope="module")
@@ -213,6 +213,12 @@ def test_oracle_preemph_matches_rtl(fvec):
     assert np.array_equal(R.preemph(fvec["preemph_in"]), fvec["preemph_out"])
 
 
+def test_oracle_power_24_bits_matches_rtl(fvec):
+    """PowerSpectrum with its class default width_output = 24 (pow2.py:44, bench at :74)."""
+    x = fvec["power24_in"]
+    assert np.array_equal(R.power_spectrum(x[:, 0], x[:, 1], 16, 24), fvec["power24_out"])
+
+
 @pytest.mark.gpu
 def test_cuda_frame_and_preemph_match_rtl(fvec):
     import torch
@@ -233,3 +239,6 @@ def test_cuda_frame_and_preemph_match_rtl(fvec):
     pre = mfcc_b200.Preemph(16, device="cuda:0")
     got = pre(torch.from_numpy(fvec["preemph_in"].astype(np.int16)).to("cuda:0")).cpu().numpy()
     assert np.array_equal(got, fvec["preemph_out"])
+    pw = mfcc_b200.PowerSpectrum(device="cuda:0")               # class defaults: width 16, 24 bits out
+    got = pw(torch.from_numpy(fvec["power24_in"].astype(np.int16)).to("cuda:0")).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32).astype(np.int64), fvec["power24_out"])
