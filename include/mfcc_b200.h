@@ -152,6 +152,14 @@ int  mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_f
 int  mfcc_b200_power(const int16_t *d_in, uint32_t *d_out, int64_t n_bins, int32_t width_output, void *stream);
 
 /*
+ * Log2Fix(width, width_output) with any widths (mfcc/core/log.py:107-139; the reference's
+ * own bench uses 37 and 20, log.py:143; MFCC uses 16 and 15): elementwise fixed-point log2
+ * with precision = width_output - ceil(log2(width)) fraction bits, log2(0) = 0.
+ */
+int  mfcc_b200_log2fix(const uint64_t *d_in, uint32_t *d_out, int64_t n, int32_t width, int32_t width_output,
+                       void *stream);
+
+/*
  * Streaming: one hop per stream per call, the mic2mfcc use of the core
  * (mfcc/targets/mic2mfcc.py:19-30).  d_state holds, per stream, the last nfft-hop
  * raw samples and the sample before them (what Preemph.odata and the Frame ring

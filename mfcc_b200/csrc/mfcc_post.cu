@@ -138,6 +138,27 @@ __global__ void k_power_general(const int16_t *f, uint32_t *pw, long long total,
     }
 }
 
+// Log2Fix(width, width_output) -> Log2FixCalc, mfcc/core/log.py:19-104, :107-139, any widths:
+// the FSM's shift-right normalisation, then precision-1 squarings of a (precision+1)-bit value
+__global__ void k_log2_general(const unsigned long long *in, unsigned *out, long long total, int precision,
+                               int width_output) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const unsigned long long v = in[i];
+        unsigned long long x = (v == 0 ? 1ull : v) << precision;          // log.py:123-126
+        unsigned long long o = 0, b = 1ull << (precision - 1);
+        while (x >> (precision + 1)) { x >>= 1; o += 1ull << precision; }  // SHIFT-RIGHT
+        unsigned long long z = x;
+        for (int cnt = precision - 1; cnt > 0; --cnt) {                   // CALC-1 / CALC-2
+            z &= (2ull << precision) - 1;                                 // the multiplier takes precision+1 bits
+            const unsigned long long c = z * z;
+            if ((c >> (2 * precision + 1)) & 1) { z = c >> (precision + 1); o += b; }
+            else z = c >> precision;
+            b >>= 1;
+        }
+        out[i] = (unsigned)(width_output >= 32 ? o : o & ((1ull << width_output) - 1));   // log.py:133
+    }
+}
+
 inline int grid_for(long long total, int block) {
     long long g = (total + block - 1) / block;
     if (g > 148 * 16) g = 148 * 16;
@@ -185,6 +206,22 @@ int mfcc_b200_power(const int16_t *d_in, uint32_t *d_out, int64_t n_bins, int32_
     if (n_bins == 0) return MFCC_B200_OK;
     if (!d_in || !d_out) return fail_ext(MFCC_B200_EINVAL, "null buffer");
     k_power_general<<<grid_for(n_bins, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n_bins, 32 - width_output);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_log2fix(const uint64_t *d_in, uint32_t *d_out, int64_t n, int32_t width, int32_t width_output, void *stream)
+{
+    if (n < 0 || width < 2 || width_output < 1 || width_output > 32) return fail_ext(MFCC_B200_EINVAL, "bad widths");
+    int lg = 0;
+    while ((1 << lg) < width) ++lg;                                   // ceil(log2(width)), log.py:114
+    const int precision = width_output - lg;
+    if (precision < 1 || precision > 30 || width + precision > 63)
+        return fail_ext(MFCC_B200_EUNSUPPORTED, "need 1 <= width_output - ceil(log2(width)) <= 30 and width + precision <= 63");
+    if (n == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_log2_general<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>((const unsigned long long *)d_in, d_out, n, precision,
+                                                                       width_output);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
 }

@@ -197,23 +197,41 @@ class FilterBank(_Stage):
 
 
 class Log2Fix(_Stage):
-    """Log2Fix(width, width_output), mfcc/core/log.py:107-116.  Elementwise,
-    int16 (16-bit unsigned) -> int16 (Q4.11)."""
+    """Log2Fix(width, width_output), mfcc/core/log.py:107-116.  Elementwise.  With the widths
+    MFCC uses (16, 15: mfcc.py:82) int16 (16-bit unsigned) -> int16 (Q4.11) through the
+    table-driven stage kernel; with any other widths int64 -> int32 through the general
+    kernel (the reference's own bench uses 37 and 20, log.py:143)."""
     stage_id = _lib.STAGE_LOG2
 
     def __init__(self, width, width_output, multiplier_cls=None, _handle=None, device=None):
-        if (width, width_output) != (16, 15):
-            raise ValueError("CUDA path covers Log2Fix(16, 15) (mfcc.py:82)")
+        import math
         self.width, self.width_output = width, width_output
-        self.precision = 11
-        self._setup(_handle, device)
+        self.precision = width_output - math.ceil(math.log2(width)) if width >= 2 else 0     # log.py:114
+        self._fast = (width, width_output) == (16, 15)
+        if self._fast:
+            self._setup(_handle, device)
+            return
+        if width < 2 or not 1 <= width_output <= 32 or not 1 <= self.precision <= 30 or width + self.precision > 63:
+            raise ValueError("Log2Fix(%d, %d): widths outside what the kernel covers" % (width, width_output))
+        if not torch.cuda.is_available():
+            raise RuntimeError("stage operators need a CUDA device: there is no CPU fallback")
+        self.device = torch.device(device if device is not None else
+                                   "cuda:%d" % torch.cuda.current_device())
 
     def __call__(self, mel):
-        nf = self._h.cfg.nfilters
-        if mel.numel() % nf:
-            raise ValueError("Log2Fix: element count must be a multiple of nfilters=%d" % nf)
-        x = self._check(mel, torch.int16, (mel.shape[-1],))
-        return self._run(x, torch.empty_like(x), x.numel() // nf)
+        if self._fast:
+            nf = self._h.cfg.nfilters
+            if mel.numel() % nf:
+                raise ValueError("Log2Fix: element count must be a multiple of nfilters=%d" % nf)
+            x = self._check(mel, torch.int16, (mel.shape[-1],))
+            return self._run(x, torch.empty_like(x), x.numel() // nf)
+        x = self._check(mel, torch.int64, (mel.shape[-1],))
+        out = torch.empty(x.shape, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_log2fix(
+                C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), x.numel(), self.width, self.width_output,
+                C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class DCTStream(_Stage):

@@ -373,6 +373,14 @@ def frame_vectors():
     simp.run()
     out["power24_in"] = pr
     out["power24_out"] = np.array(gotp, dtype=np.int64)
+
+    # Log2Fix(37, 20), the reference's own bench (log.py:143-149: the value 2207315)
+    with contextlib.redirect_stdout(io.StringIO()):
+        from mfcc.core.log import Log2Fix
+    vals = np.array([2207315, 0, 1, 2, 3, 255, 256, (1 << 37) - 1, 1 << 36, 1 << 20, 12345678901]
+                    + [int(v) for v in rng.integers(1, 1 << 37, 21)], dtype=np.int64)
+    out["log2_37_20_in"] = vals
+    out["log2_37_20_out"] = _stream_stage(Log2Fix(37, 20, multiplier_cls=Multiplier), vals[None, :])[0, :, 0]
     return out
 
 

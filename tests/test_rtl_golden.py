@@ -219,6 +219,13 @@ def test_oracle_power_24_bits_matches_rtl(fvec):
     assert np.array_equal(R.power_spectrum(x[:, 0], x[:, 1], 16, 24), fvec["power24_out"])
 
 
+def test_oracle_log2_37_20_matches_rtl(fvec):
+    """Log2Fix(37, 20): the widths and the value (2207315) of the reference's own bench, log.py:143-149."""
+    assert np.array_equal(R.log2fix(fvec["log2_37_20_in"], 37, 20), fvec["log2_37_20_out"])
+    v = int(R.log2fix(np.array([2207315]), 37, 20)[0])
+    assert abs(v / 2 ** 14 - np.log2(2207315)) < 2e-3          # the bench prints res / 2**precision
+
+
 @pytest.mark.gpu
 def test_cuda_frame_and_preemph_match_rtl(fvec):
     import torch
@@ -239,6 +246,11 @@ def test_cuda_frame_and_preemph_match_rtl(fvec):
     pre = mfcc_b200.Preemph(16, device="cuda:0")
     got = pre(torch.from_numpy(fvec["preemph_in"].astype(np.int16)).to("cuda:0")).cpu().numpy()
     assert np.array_equal(got, fvec["preemph_out"])
+    lg = mfcc_b200.Log2Fix(37, 20, device="cuda:0")             # log.py:143
+    got = lg(torch.from_numpy(fvec["log2_37_20_in"]).to("cuda:0")).cpu().numpy()
+    assert np.array_equal(got.astype(np.int64), fvec["log2_37_20_out"])
+    with pytest.raises(ValueError):
+        mfcc_b200.Log2Fix(16, 3, device="cuda:0")               # no fraction bits left
     pw = mfcc_b200.PowerSpectrum(device="cuda:0")               # class defaults: width 16, 24 bits out
     got = pw(torch.from_numpy(fvec["power24_in"].astype(np.int16)).to("cuda:0")).cpu().numpy()
     assert np.array_equal(got.view(np.uint32).astype(np.int64), fvec["power24_out"])
