@@ -160,6 +160,18 @@ int  mfcc_b200_log2fix(const uint64_t *d_in, uint32_t *d_out, int64_t n, int32_t
                        void *stream);
 
 /*
+ * FilterBank with any parameter set (mfcc/core/filterbank.py:37-63; the class defaults are
+ * width 24 / output 24 / 16 taps, the reference's own bench uses width 31 / output 32,
+ * filterbank.py:148; MFCC uses 30 / 16 / gain 18): the register-level algorithm of
+ * filterbank.py:90-142 on d_power [n_frames][nbins] (width-bit unsigned values), giving
+ * d_out [n_frames][ntap].  d_steps[nsteps] is the table of calc_filters() (:22-34) for the
+ * filter points, maxvalrange and lo_bit = maxvalrange - (gain + width_output) as at :71, :122.
+ */
+int  mfcc_b200_filterbank(const uint32_t *d_power, uint32_t *d_out, int64_t n_frames, int32_t nbins, int32_t ntap,
+                          int32_t width_mul, int32_t maxvalrange, int32_t lo_bit, int32_t width_output,
+                          const uint64_t *d_steps, int32_t nsteps, void *stream);
+
+/*
  * Streaming: one hop per stream per call, the mic2mfcc use of the core
  * (mfcc/targets/mic2mfcc.py:19-30).  d_state holds, per stream, the last nfft-hop
  * raw samples and the sample before them (what Preemph.odata and the Frame ring

@@ -86,6 +86,8 @@ def lib():
     L.mfcc_b200_power.argtypes = [vp, vp, i64, i32, vp]
     L.mfcc_b200_log2fix.restype = C.c_int
     L.mfcc_b200_log2fix.argtypes = [vp, vp, i64, i32, i32, vp]
+    L.mfcc_b200_filterbank.restype = C.c_int
+    L.mfcc_b200_filterbank.argtypes = [vp, vp, i64, i32, i32, i32, i32, i32, i32, vp, i32, vp]
     L.mfcc_b200_to_int16.restype = C.c_int
     L.mfcc_b200_to_int16.argtypes = [vp, vp, i64, vp]
     L.mfcc_b200_uart_frame.restype = C.c_int
@@ -113,7 +115,7 @@ def lib():
 
 
 EXPORTS = ["mfcc_b200_create", "mfcc_b200_destroy", "mfcc_b200_run", "mfcc_b200_run_host",
-           "mfcc_b200_stage", "mfcc_b200_frame", "mfcc_b200_power", "mfcc_b200_log2fix", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_lifter",
+           "mfcc_b200_stage", "mfcc_b200_frame", "mfcc_b200_power", "mfcc_b200_log2fix", "mfcc_b200_filterbank", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_lifter",
            "mfcc_b200_standardize", "mfcc_b200_to_int16", "mfcc_b200_uart_frame", "mfcc_b200_vad_step",
            "mfcc_b200_librosa_create", "mfcc_b200_librosa_destroy", "mfcc_b200_librosa_frames",
            "mfcc_b200_librosa_workspace", "mfcc_b200_librosa_run",

@@ -159,6 +159,49 @@ __global__ void k_log2_general(const unsigned long long *in, unsigned *out, long
     }
 }
 
+// FilterBank with any parameter set (mfcc/core/filterbank.py:37-144), register by register:
+// the 2*wm-bit weight generator (:90-115) and the two maxvalrange-bit accumulators
+// (:119-134), output taken from o_regb before the update and suppressed for segment 0
+// (:139-140).  One thread per frame, 128-bit registers (maxvalrange reaches 68 bits for the
+// reference bench's FilterBank(31, 32)).  Frames are independent: `last` clears the
+// generator and the first peak of the next frame overwrites o_regb.
+__global__ void k_filterbank_general(const uint32_t *power, uint32_t *out, long long n_frames, int nbins, int ntap,
+                                     int wm, int maxvalrange, int lo_bit, int width_output,
+                                     const unsigned long long *steps, int nsteps) {
+    typedef unsigned __int128 u128;
+    const u128 rmask = maxvalrange >= 128 ? ~(u128)0 : (((u128)1 << maxvalrange) - 1);
+    const unsigned long long amask = (2 * wm >= 64) ? ~0ull : ((1ull << (2 * wm)) - 1);
+    const unsigned long long top = (1ull << wm) - 1;
+    const u128 omask = (((u128)1 << width_output) - 1);
+    for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < n_frames; k += (long long)gridDim.x * blockDim.x) {
+        const uint32_t *p = power + k * nbins;
+        uint32_t *o = out + k * ntap;
+        unsigned long long acc = 0;
+        int adr = 0, nout = 0;
+        u128 rega = 0, regb = 0;
+        for (int b = 0; b < nbins; ++b) {
+            const unsigned long long d = p[b];
+            const bool last = b == nbins - 1;
+            const unsigned long long w = acc >> wm;
+            const bool highest = w == top;
+            const u128 c = (u128)d * w;
+            const int adr0 = adr;
+            if (highest || last) { adr = last ? 0 : adr + 1; acc = 0; }
+            else acc = (acc + (adr < nsteps ? steps[adr] : 0ull)) & amask;
+            const uint32_t o_data = (uint32_t)((regb >> lo_bit) & omask);
+            if (highest || last) {
+                if (adr0 != 0 && nout < ntap) o[nout++] = o_data;
+                regb = (rega + ((u128)d << wm)) & rmask;
+                rega = 0;
+            } else {
+                rega = (rega + c) & rmask;
+                regb = (regb + ((u128)d << wm) - c) & rmask;
+            }
+        }
+        for (; nout < ntap; ++nout) o[nout] = 0;
+    }
+}
+
 inline int grid_for(long long total, int block) {
     long long g = (total + block - 1) / block;
     if (g > 148 * 16) g = 148 * 16;
@@ -222,6 +265,23 @@ int mfcc_b200_log2fix(const uint64_t *d_in, uint32_t *d_out, int64_t n, int32_t 
     if (!d_in || !d_out) return fail_ext(MFCC_B200_EINVAL, "null buffer");
     k_log2_general<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>((const unsigned long long *)d_in, d_out, n, precision,
                                                                        width_output);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_filterbank(const uint32_t *d_power, uint32_t *d_out, int64_t n_frames, int32_t nbins, int32_t ntap,
+                         int32_t width_mul, int32_t maxvalrange, int32_t lo_bit, int32_t width_output,
+                         const uint64_t *d_steps, int32_t nsteps, void *stream)
+{
+    if (n_frames < 0 || nbins < 1 || ntap < 1 || nsteps < 1) return fail_ext(MFCC_B200_EINVAL, "bad size");
+    if (width_mul < 1 || width_mul > 31 || width_output < 1 || width_output > 32 || maxvalrange < 1 || maxvalrange > 127 ||
+        lo_bit < 0 || lo_bit + width_output > 128)
+        return fail_ext(MFCC_B200_EUNSUPPORTED, "need width_mul <= 31, width_output <= 32, maxvalrange <= 127");
+    if (n_frames == 0) return MFCC_B200_OK;
+    if (!d_power || !d_out || !d_steps) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_filterbank_general<<<grid_for(n_frames, 128), 128, 0, (cudaStream_t)stream>>>(
+        d_power, d_out, n_frames, nbins, ntap, width_mul, maxvalrange, lo_bit, width_output,
+        (const unsigned long long *)d_steps, nsteps);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
 }

@@ -167,33 +167,61 @@ class PowerSpectrum(_Stage):
 
 class FilterBank(_Stage):
     """FilterBank(width=24, width_output=24, width_mul=None, gain=0, sample_rate=16000,
-    nfft=512, ntap=16), mfcc/core/filterbank.py:37-63.  int32 [K, 256] -> int16 [K, ntap]
-    (16-bit unsigned values that wrap, filterbank.py:122)."""
+    nfft=512, ntap=16), mfcc/core/filterbank.py:37-63.  With the parameters MFCC uses
+    (30, 16, gain 18, 16 or 32 taps: mfcc.py:69-75) int32 [K, 256] -> int16 [K, ntap]
+    (16-bit unsigned values that wrap, filterbank.py:122) through the warp-per-frame stage
+    kernel; with any other parameter set int32 [K, nfft/2] -> int32 [K, ntap] (the unsigned
+    width_output-bit values) through the general register-level kernel."""
     stage_id = _lib.STAGE_MEL
 
     def __init__(self, width=24, width_output=24, width_mul=None, gain=0, sample_rate=16000,
                  nfft=512, ntap=16, multiplier_cls=None, _handle=None, device=None):
+        import math
+        from . import tables
         width_mul = width if width_mul is None else width_mul
-        if (width, width_output, width_mul, gain, nfft) != (30, 16, 30, 18, 512) or \
-                ntap not in (16, 32):
-            raise ValueError("CUDA path covers FilterBank(30, 16, gain=18, nfft=512, ntap 16|32) "
-                             "(mfcc.py:69-75)")
         self.width, self.width_output, self.width_mul, self.gain = width, width_output, width_mul, gain
         self.sample_rate, self.nfft, self.ntap = sample_rate, nfft, ntap
-        if _handle is not None and (_handle.cfg.nfilters != ntap or
-                                    _handle.cfg.samplerate != sample_rate):
-            _handle = None
-        if _handle is None and torch.cuda.is_available():
-            dev = torch.device(device if device is not None else
-                               "cuda:%d" % torch.cuda.current_device())
-            with torch.cuda.device(dev):
-                _handle = Handle(MFCCConfig(samplerate=sample_rate, nfilters=ntap, nceptrums=ntap))
-        self._setup(_handle, device, ntap)
+        self._fast = (width, width_output, width_mul, gain, nfft) == (30, 16, 30, 18, 512) and ntap in (16, 32)
+        if self._fast:
+            if _handle is not None and (_handle.cfg.nfilters != ntap or
+                                        _handle.cfg.samplerate != sample_rate):
+                _handle = None
+            if _handle is None and torch.cuda.is_available():
+                dev = torch.device(device if device is not None else
+                                   "cuda:%d" % torch.cuda.current_device())
+                with torch.cuda.device(dev):
+                    _handle = Handle(MFCCConfig(samplerate=sample_rate, nfilters=ntap, nceptrums=ntap))
+            self._setup(_handle, device, ntap)
+            return
+        if not (1 <= width <= 31 and 1 <= width_mul <= 31 and 1 <= width_output <= 32 and ntap >= 1):
+            raise ValueError("FilterBank: width and width_mul must be <= 31, width_output <= 32")
+        if not torch.cuda.is_available():
+            raise RuntimeError("stage operators need a CUDA device: there is no CPU fallback")
+        self.device = torch.device(device if device is not None else
+                                   "cuda:%d" % torch.cuda.current_device())
+        pts = tables.mel_points(ntap, nfft, sample_rate)
+        steps = tables.mel_steps(pts, wsize=width_mul)                       # calc_filters, filterbank.py:22-34
+        self.maxvalrange = int(math.log2(pts[-1] - pts[-3])) + width + width_mul       # :71
+        self.lo_bit = self.maxvalrange - (gain + width_output)                         # :122
+        if self.lo_bit < 0 or self.maxvalrange > 127:
+            raise ValueError("FilterBank: gain + width_output exceeds the accumulator width")
+        self._steps = torch.tensor([int(v) for v in steps], dtype=torch.int64, device=self.device)
 
     def __call__(self, power):
-        x = self._check(power, torch.int32, (256,))
-        out = torch.empty(x.shape[:-1] + (self.ntap,), dtype=torch.int16, device=self.device)
-        return self._run(x, out, x.numel() // 256)
+        if self._fast:
+            x = self._check(power, torch.int32, (256,))
+            out = torch.empty(x.shape[:-1] + (self.ntap,), dtype=torch.int16, device=self.device)
+            return self._run(x, out, x.numel() // 256)
+        nb = self.nfft // 2
+        x = self._check(power, torch.int32, (nb,))
+        out = torch.empty(x.shape[:-1] + (self.ntap,), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_filterbank(
+                C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), x.numel() // nb, nb, self.ntap,
+                self.width_mul, self.maxvalrange, self.lo_bit, self.width_output,
+                C.c_void_p(self._steps.data_ptr()), self._steps.numel(),
+                C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class Log2Fix(_Stage):

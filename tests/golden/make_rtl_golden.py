@@ -381,6 +381,18 @@ def frame_vectors():
                     + [int(v) for v in rng.integers(1, 1 << 37, 21)], dtype=np.int64)
     out["log2_37_20_in"] = vals
     out["log2_37_20_out"] = _stream_stage(Log2Fix(37, 20, multiplier_cls=Multiplier), vals[None, :])[0, :, 0]
+
+    # FilterBank with the widths of the reference's own bench (filterbank.py:148: width 31, output 32,
+    # constant input 1234) and with the class defaults (24 / 24 / 16 taps, filterbank.py:38-48)
+    with contextlib.redirect_stdout(io.StringIO()):
+        from mfcc.core.filterbank import FilterBank
+    rows = np.stack([np.full(256, 1234), rng.integers(0, 1 << 31, 256), np.full(256, (1 << 31) - 1),
+                     np.zeros(256, dtype=np.int64), rng.integers(0, 1 << 12, 256)])
+    out["mel_31_32_in"] = rows
+    out["mel_31_32_out"] = _stream_stage(FilterBank(width=31, width_output=32, multiplier_cls=Multiplier), rows)[:, :, 0]
+    rows = np.stack([np.full(256, 1234), rng.integers(0, 1 << 24, 256), np.full(256, (1 << 24) - 1)])
+    out["mel_default_in"] = rows
+    out["mel_default_out"] = _stream_stage(FilterBank(multiplier_cls=Multiplier), rows)[:, :, 0]
     return out
 
 

@@ -226,6 +226,15 @@ def test_oracle_log2_37_20_matches_rtl(fvec):
     assert abs(v / 2 ** 14 - np.log2(2207315)) < 2e-3          # the bench prints res / 2**precision
 
 
+def test_oracle_filterbank_other_widths_matches_rtl(fvec):
+    """FilterBank(31, 32) (the reference's own bench, filterbank.py:148, 68-bit accumulators) and
+    FilterBank() with the class defaults (24 / 24 / gain 0 / 16 taps)."""
+    got = R.filterbank(fvec["mel_31_32_in"], width=31, width_output=32, gain=0, sample_rate=16000, nfft=512, ntap=16)
+    assert np.array_equal(got, fvec["mel_31_32_out"])
+    got = R.filterbank(fvec["mel_default_in"], width=24, width_output=24, gain=0, sample_rate=16000, nfft=512, ntap=16)
+    assert np.array_equal(got, fvec["mel_default_out"])
+
+
 @pytest.mark.gpu
 def test_cuda_frame_and_preemph_match_rtl(fvec):
     import torch
@@ -246,6 +255,12 @@ def test_cuda_frame_and_preemph_match_rtl(fvec):
     pre = mfcc_b200.Preemph(16, device="cuda:0")
     got = pre(torch.from_numpy(fvec["preemph_in"].astype(np.int16)).to("cuda:0")).cpu().numpy()
     assert np.array_equal(got, fvec["preemph_out"])
+    fb = mfcc_b200.FilterBank(width=31, width_output=32, device="cuda:0")            # filterbank.py:148
+    got = fb(torch.from_numpy(fvec["mel_31_32_in"].astype(np.int32)).to("cuda:0")).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32).astype(np.int64), fvec["mel_31_32_out"])
+    fb = mfcc_b200.FilterBank(device="cuda:0")                                       # class defaults
+    got = fb(torch.from_numpy(fvec["mel_default_in"].astype(np.int32)).to("cuda:0")).cpu().numpy()
+    assert np.array_equal(got.view(np.uint32).astype(np.int64), fvec["mel_default_out"])
     lg = mfcc_b200.Log2Fix(37, 20, device="cuda:0")             # log.py:143
     got = lg(torch.from_numpy(fvec["log2_37_20_in"]).to("cuda:0")).cpu().numpy()
     assert np.array_equal(got.astype(np.int64), fvec["log2_37_20_out"])
