@@ -188,6 +188,14 @@ int  mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n
                     void *d_out, void *stream);
 
 /*
+ * The same step with HOST buffers and the state kept inside the handle: what a plain-C host
+ * without CUDA headers binds in place of the microphone front end (host/mic2mfcc.c).
+ * The state is (re)allocated and zeroed when n_streams changes or reset != 0; h_hop == NULL
+ * resets only.  Synchronous: returns when h_out [n_streams][nceptrums] is complete.
+ */
+int  mfcc_b200_step_host(void *handle, int32_t n_streams, const int16_t *h_hop, void *h_out, int32_t reset);
+
+/*
  * ---- the steps after the path in the reference's tool chain ----
  * All buffers are device pointers owned by the caller.
  *

@@ -511,6 +511,10 @@ struct Handle {
     int16_t *d_in[2] = {nullptr, nullptr};
     void *d_out[2] = {nullptr, nullptr};
     size_t in_cap = 0, out_cap = 0;
+    // state and staging of mfcc_b200_step_host
+    void *s_state = nullptr, *s_out = nullptr;
+    int16_t *s_hop = nullptr;
+    int s_streams = 0;
 };
 
 // Which twiddle each DCT lane needs: ownership of positions through the 2NF-point
@@ -800,6 +804,9 @@ void mfcc_b200_destroy(void *handle)
         if (h->d_in[i]) cudaFree(h->d_in[i]);
         if (h->d_out[i]) cudaFree(h->d_out[i]);
     }
+    if (h->s_state) cudaFree(h->s_state);
+    if (h->s_hop) cudaFree(h->s_hop);
+    if (h->s_out) cudaFree(h->s_out);
     if (h->d_tab) cudaFree(h->d_tab);
     if (h->d_ftab) cudaFree(h->d_ftab);
     delete h;
@@ -985,6 +992,38 @@ int mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n_
                                                                    h->cfg.nceptrums, h->d_tab);
     g_launches.fetch_add(1);
     CUDA_TRY(cudaGetLastError());
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_step_host(void *handle, int32_t n_streams, const int16_t *h_hop, void *h_out, int32_t reset)
+{
+    if (int rc = check_handle(handle)) return rc;
+    Handle *h = static_cast<Handle *>(handle);
+    if (n_streams < 1) return fail(MFCC_B200_EINVAL, "n_streams must be >= 1");
+    const size_t esz = h->cfg.mode == MFCC_B200_MODE_FP32 ? sizeof(float) : sizeof(int16_t);
+    const size_t state_bytes = (size_t)n_streams * STATE_N * sizeof(int16_t);
+    if (!h->st[0]) CUDA_TRY(cudaStreamCreateWithFlags(&h->st[0], cudaStreamNonBlocking));
+    if (h->s_streams != n_streams) {
+        if (h->s_state) cudaFree(h->s_state);
+        if (h->s_hop) cudaFree(h->s_hop);
+        if (h->s_out) cudaFree(h->s_out);
+        h->s_state = h->s_out = nullptr; h->s_hop = nullptr; h->s_streams = 0;
+        CUDA_TRY(cudaMalloc(&h->s_state, state_bytes));
+        CUDA_TRY(cudaMalloc(&h->s_hop, (size_t)n_streams * HOP * sizeof(int16_t)));
+        CUDA_TRY(cudaMalloc(&h->s_out, (size_t)n_streams * h->cfg.nceptrums * esz));
+        h->s_streams = n_streams;
+        reset = 1;
+    }
+    if (reset) CUDA_TRY(cudaMemsetAsync(h->s_state, 0, state_bytes, h->st[0]));      // the reset of every stream
+    if (!h_hop) {                                                                    // reset only
+        CUDA_TRY(cudaStreamSynchronize(h->st[0]));
+        return MFCC_B200_OK;
+    }
+    if (!h_out) return fail(MFCC_B200_EINVAL, "null buffer");
+    CUDA_TRY(cudaMemcpyAsync(h->s_hop, h_hop, (size_t)n_streams * HOP * sizeof(int16_t), cudaMemcpyHostToDevice, h->st[0]));
+    if (int rc = mfcc_b200_step(h, h->s_state, h->s_hop, n_streams, h->s_out, h->st[0])) return rc;
+    CUDA_TRY(cudaMemcpyAsync(h_out, h->s_out, (size_t)n_streams * h->cfg.nceptrums * esz, cudaMemcpyDeviceToHost, h->st[0]));
+    CUDA_TRY(cudaStreamSynchronize(h->st[0]));
     return MFCC_B200_OK;
 }
 

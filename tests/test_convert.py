@@ -229,3 +229,31 @@ def test_c_host_tool_writes_the_reference_tools_files(tmp_path, wav):
         assert a == b and len(a) > 0, rel
     assert os.path.getsize(os.path.join(c_root, "empty.mfcc")) == 64          # one zero-filled round
     assert not os.path.exists(os.path.join(c_root, "t", "rate.mfcc"))
+
+
+@pytest.mark.gpu
+def test_c_mic_tool_feeds_the_reference_receiver(tmp_path):
+    """host/mic2mfcc.c (plain C over mfcc_b200_step_host): its byte stream is what the mic
+    build sends (magic.py:27-39), column k = the batch path's frame k, and the reference's
+    own receiver (software/cepstrum.c:15-68, restated in oracle/ref_recv.py) parses it."""
+    import subprocess
+    from oracle import ref_np, ref_recv as RR
+    tool = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "host", "mic2mfcc")
+    if not os.path.exists(tool):
+        pytest.fail("host/mic2mfcc not built (python -c 'import __graft_entry__ as g; g.build()')")
+    rng = np.random.default_rng(77)
+    x = rng.integers(-20000, 20000, size=512 + 170 * 99 + 57, dtype=np.int16)
+    r = subprocess.run([tool, "16"], input=x.astype("<i2").tobytes(), capture_output=True, timeout=120)
+    assert r.returncode == 0, r.stderr.decode()
+    wire = np.frombuffer(r.stdout, dtype=np.uint8)
+    want = ref_np.mfcc(x, nfilters=32, nceptrums=16, n_frames=100)
+    assert wire.size == 100 * 34
+    words = wire.reshape(100, 17, 2)
+    got = ((words[:, :, 0].astype(np.uint16) << 8) | words[:, :, 1]).astype(np.uint16)
+    assert (got[:, 0] == 0xa55a).all()
+    np.testing.assert_array_equal(got[:, 1:].view(np.int16), want)
+    # through the receiver: it fills its 93-column window from the start of the stream
+    if not RR.available():
+        pytest.fail("oracle/_ref/libcepstrum_ref.so missing: build() compiles it where /root/reference exists")
+    win = RR.get_window(wire.tobytes(), 16, 93)
+    np.testing.assert_array_equal(win, want[:93])
