@@ -160,6 +160,29 @@ int  mfcc_b200_log2fix(const uint64_t *d_in, uint32_t *d_out, int64_t n, int32_t
                        void *stream);
 
 /*
+ * WindowHamming(16, nfft, precision) with any nfft >= 8 (mfcc/core/window.py:10-20, :74-84):
+ * d_out[r][n] = top 16 bits of d_in[r][n] * d_curve[n], d_curve[nfft] the multipliers the
+ * quarter table decodes to (mfcc_b200.tables.window_curve).
+ */
+int  mfcc_b200_window(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t nfft, int32_t precision,
+                      const uint16_t *d_curve, void *stream);
+
+/*
+ * FftStream(16, nfft) and DCTStream(16, nfft) with any power-of-two size (mfcc/core/
+ * fft_stream.py:6-38, nfft 32..4096: d_in [n_rows][nfft] real -> d_out [n_rows][nfft/2][2];
+ * mfcc/core/dct_stream.py:6-37, nfft 8..1024 inputs: d_in [n_rows][nfft] -> d_out
+ * [n_rows][nfft], through the 4*nfft-point FFT of :29-34).  Both run the FFT core of
+ * mfcc/misc/fft.py with its rounding butterfly; d_twiddle is the decoded twiddle ROM of that
+ * core, int16 [size/2][2] = W(k) (re, im), size = nfft or 4*nfft (tables.twiddle_table).
+ * Sizes below 32 points are refused: the reference's scheduler reads a stage's operands
+ * before the previous stage has written them there (mfcc/misc/fft.py:251-308, :344).
+ */
+int  mfcc_b200_fft_stream(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t nfft,
+                          const int16_t *d_twiddle, void *stream);
+int  mfcc_b200_dct_stream(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t nfft,
+                          const int16_t *d_twiddle, void *stream);
+
+/*
  * FilterBank with any parameter set (mfcc/core/filterbank.py:37-63; the class defaults are
  * width 24 / output 24 / 16 taps, the reference's own bench uses width 31 / output 32,
  * filterbank.py:148; MFCC uses 30 / 16 / gain 18): the register-level algorithm of

@@ -76,6 +76,12 @@ def lib():
     L.mfcc_b200_state_bytes.argtypes = [vp, i32, C.POINTER(i64)]
     L.mfcc_b200_step.restype = C.c_int
     L.mfcc_b200_step.argtypes = [vp, vp, vp, i32, vp, vp]
+    for name in ("mfcc_b200_fft_stream", "mfcc_b200_dct_stream"):
+        f = getattr(L, name)
+        f.restype = C.c_int
+        f.argtypes = [vp, vp, i64, i32, vp, vp]
+    L.mfcc_b200_window.restype = C.c_int
+    L.mfcc_b200_window.argtypes = [vp, vp, i64, i32, i32, vp, vp]
     L.mfcc_b200_step_host.restype = C.c_int
     L.mfcc_b200_step_host.argtypes = [vp, i32, vp, vp, i32]
     L.mfcc_b200_lifter.restype = C.c_int
@@ -117,7 +123,8 @@ def lib():
 
 
 EXPORTS = ["mfcc_b200_create", "mfcc_b200_destroy", "mfcc_b200_run", "mfcc_b200_run_host",
-           "mfcc_b200_stage", "mfcc_b200_frame", "mfcc_b200_power", "mfcc_b200_log2fix", "mfcc_b200_filterbank", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_step_host", "mfcc_b200_lifter",
+           "mfcc_b200_stage", "mfcc_b200_frame", "mfcc_b200_window", "mfcc_b200_fft_stream",
+           "mfcc_b200_dct_stream", "mfcc_b200_power", "mfcc_b200_log2fix", "mfcc_b200_filterbank", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_step_host", "mfcc_b200_lifter",
            "mfcc_b200_standardize", "mfcc_b200_to_int16", "mfcc_b200_uart_frame", "mfcc_b200_vad_step",
            "mfcc_b200_librosa_create", "mfcc_b200_librosa_destroy", "mfcc_b200_librosa_frames",
            "mfcc_b200_librosa_workspace", "mfcc_b200_librosa_run",

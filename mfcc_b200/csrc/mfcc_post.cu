@@ -202,6 +202,62 @@ __global__ void k_filterbank_general(const uint32_t *power, uint32_t *out, long 
     }
 }
 
+// WindowHamming(16, nfft, precision), mfcc/core/window.py:74-75, :84: the top 16 bits of the
+// signed16 x unsigned(precision+1) product, curve[] from the caller (tables.window_curve).
+__global__ void k_window_general(const int16_t *in, int16_t *out, long long total, int nfft, int shift,
+                                 const uint16_t *curve) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+        out[i] = (int16_t)(((int)in[i] * (int)curve[i & (nfft - 1)]) >> shift);
+}
+
+// The FFT core of mfcc/misc/fft.py for any power-of-two size (32..4096; below 32 points the
+// reference's scheduler has a read-before-write hazard, not reproduced), width 16: bit-reversed
+// load (:413-418), log2(size) in-place stages of the rounding butterfly
+//   t = (x1 * w + 8191) >> 14,  y0 = wrap16((x0 + t) >> 1),  y1 = wrap16((x0 - t) >> 1)
+// (:93-96, :140-192), twiddle address k * (size/2 >> stage) (:310-316).  One CTA per row, the
+// row in shared memory as packed (re, im) halves.  DCT = false: FftStream (fft_stream.py:30-38),
+// real input [size], bins 0..size/2-1 out as (re, im).  DCT = true: DCTStream(16, size/4)
+// (dct_stream.py:23-37), input L[size/4] placed at v[2n+1] and v[size-1-2n], real part of
+// bins 0..size/4-1 out.
+template <bool DCT>
+__global__ void k_fft_general(const int16_t *in, int16_t *out, long long n_rows, int nb, const short2 *tw) {
+    extern __shared__ unsigned v[];
+    const int size = 1 << nb, half = size >> 1;
+    const int n_in = DCT ? size >> 2 : size, n_out = DCT ? size >> 2 : half;
+    for (long long row = blockIdx.x; row < n_rows; row += gridDim.x) {
+        const int16_t *src = in + row * n_in;
+        for (int n = threadIdx.x; n < size; n += blockDim.x) {
+            int val;
+            if (DCT) val = (n & 1) ? src[n < half ? (n >> 1) : ((size - 1 - n) >> 1)] : 0;
+            else val = src[n];
+            v[__brev((unsigned)n) >> (32 - nb)] = (unsigned)val & 0xffffu;          // imag = 0
+        }
+        __syncthreads();
+        for (int s = 0; s < nb; ++s) {
+            for (int b = threadIdx.x; b < half; b += blockDim.x) {
+                const int k = b & ((1 << s) - 1);
+                const int p0 = ((b >> s) << (s + 1)) + k, p1 = p0 + (1 << s);
+                const short2 w = tw[k << (nb - 1 - s)];
+                const unsigned a = v[p0], c = v[p1];
+                const int x0r = (int16_t)(a & 0xffffu), x0i = (int)a >> 16;
+                const int x1r = (int16_t)(c & 0xffffu), x1i = (int)c >> 16;
+                const int tr = (x1r * w.x - x1i * w.y + 8191) >> 14;
+                const int ti = (x1r * w.y + x1i * w.x + 8191) >> 14;
+                v[p0] = ((unsigned)((x0r + tr) >> 1) & 0xffffu) | ((unsigned)((x0i + ti) >> 1) << 16);
+                v[p1] = ((unsigned)((x0r - tr) >> 1) & 0xffffu) | ((unsigned)((x0i - ti) >> 1) << 16);
+            }
+            __syncthreads();
+        }
+        if (DCT) {
+            for (int n = threadIdx.x; n < n_out; n += blockDim.x) out[row * n_out + n] = (int16_t)(v[n] & 0xffffu);
+        } else {
+            unsigned *dst = reinterpret_cast<unsigned *>(out) + row * n_out;         // (re, im) pairs
+            for (int n = threadIdx.x; n < n_out; n += blockDim.x) dst[n] = v[n];
+        }
+        __syncthreads();
+    }
+}
+
 inline int grid_for(long long total, int block) {
     long long g = (total + block - 1) / block;
     if (g > 148 * 16) g = 148 * 16;
@@ -241,6 +297,50 @@ int mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_fr
                                                                                     stepsize, nfft);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
+}
+
+int mfcc_b200_window(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t nfft, int32_t precision,
+                     const uint16_t *d_curve, void *stream)
+{
+    if (n_rows < 0 || nfft < 8 || (nfft & (nfft - 1)) || precision < 1 || precision > 14)
+        return fail_ext(MFCC_B200_EINVAL, "need n_rows >= 0, nfft a power of two >= 8 and 1 <= precision <= 14");
+    if (n_rows == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out || !d_curve) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    k_window_general<<<grid_for(n_rows * nfft, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n_rows * nfft, nfft,
+                                                                                        precision + 1, d_curve);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+static int fft_general(bool dct, const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t size,
+                       const int16_t *d_twiddle, void *stream)
+{
+    if (n_rows < 0 || size < 32 || size > 4096 || (size & (size - 1)))
+        return fail_ext(MFCC_B200_EINVAL, dct ? "need n_rows >= 0 and nfft a power of two in 8..1024"
+                                              : "need n_rows >= 0 and nfft a power of two in 32..4096");
+    if (n_rows == 0) return MFCC_B200_OK;
+    if (!d_in || !d_out || !d_twiddle) return fail_ext(MFCC_B200_EINVAL, "null buffer");
+    if (((uintptr_t)d_twiddle | (uintptr_t)d_out) & 3) return fail_ext(MFCC_B200_EINVAL, "d_twiddle and d_out must be 4-byte aligned");
+    int nb = 0;
+    while ((1 << nb) < size) ++nb;
+    const int threads = size / 2 < 256 ? (size / 2 < 32 ? 32 : size / 2) : 256;
+    const int grid = (int)(n_rows < 148 * 16 ? n_rows : 148 * 16);
+    const size_t smem = (size_t)size * sizeof(unsigned);
+    if (dct) k_fft_general<true><<<grid, threads, smem, (cudaStream_t)stream>>>(d_in, d_out, n_rows, nb, (const short2 *)d_twiddle);
+    else k_fft_general<false><<<grid, threads, smem, (cudaStream_t)stream>>>(d_in, d_out, n_rows, nb, (const short2 *)d_twiddle);
+    POST_LAUNCH_CHECK();
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_fft_stream(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t nfft, const int16_t *d_twiddle, void *stream)
+{
+    return fft_general(false, d_in, d_out, n_rows, nfft, d_twiddle, stream);
+}
+
+int mfcc_b200_dct_stream(const int16_t *d_in, int16_t *d_out, int64_t n_rows, int32_t nfft, const int16_t *d_twiddle, void *stream)
+{
+    if (nfft < 8 || nfft > 1024) return fail_ext(MFCC_B200_EINVAL, "need n_rows >= 0 and nfft a power of two in 8..1024");
+    return fft_general(true, d_in, d_out, n_rows, 4 * nfft, d_twiddle, stream);
 }
 
 int mfcc_b200_power(const int16_t *d_in, uint32_t *d_out, int64_t n_bins, int32_t width_output, void *stream)

@@ -1,7 +1,9 @@
 """One callable per stage module of the reference, same constructor names and
-defaults; each maps a GPU tensor to a GPU tensor through
-``mfcc_b200_stage``.  Only the parameter combinations MFCC.elaborate can generate
-(/root/reference/mfcc/core/mfcc.py:38-88) have a CUDA path; others raise ValueError.
+defaults; each maps a GPU tensor to a GPU tensor.  The parameter
+combinations MFCC.elaborate generates (/root/reference/mfcc/core/mfcc.py:38-88) run the
+stage kernels that share their device code with the fused kernel (``mfcc_b200_stage``);
+other parameter sets of the same classes run handle-free general kernels.  Width is 16
+throughout, as everywhere in the reference.
 
 16-bit unsigned streams (mel, log) are carried in int16 tensors and 30-bit powers in
 int32 tensors: same bits, torch has no general uint16/uint32 arithmetic.
@@ -12,9 +14,15 @@ import ctypes as C
 
 import torch
 
-from . import _lib
+from . import _lib, tables
 from .config import MFCCConfig
 from .handle import Handle
+
+
+# mfcc/misc/fft.py:251-308, :344: a stage lasts size/2 cycles, a butterfly's results land 8
+# cycles after its read; tests/test_rtl_golden.py::test_small_fft_hazard_of_the_reference
+_HAZARD = ("a %d-point FFT core: below 32 points the reference's scheduler has a read-before-write "
+           "hazard and its output is not a transform; not reproduced")
 
 
 class _Stage:
@@ -29,6 +37,13 @@ class _Stage:
             with torch.cuda.device(self.device):
                 handle = Handle(MFCCConfig(nfilters=nfilters, nceptrums=nfilters))
         self._h = handle
+
+    def _general_device(self, device):
+        """Handle-free operators (the general kernels take their tables per call)."""
+        if not torch.cuda.is_available():
+            raise RuntimeError("stage operators need a CUDA device: there is no CPU fallback")
+        self.device = torch.device(device if device is not None else
+                                   "cuda:%d" % torch.cuda.current_device())
 
     def _check(self, x, dtype, last_dims):
         if not isinstance(x, torch.Tensor) or x.dtype != dtype:
@@ -103,39 +118,76 @@ class Frame(_Stage):
 
 
 class WindowHamming(_Stage):
-    """WindowHamming(width=16, nfft=512, precision=8), mfcc/core/window.py:10-20."""
+    """WindowHamming(width=16, nfft=512, precision=8), mfcc/core/window.py:10-20, any
+    power-of-two nfft >= 8 and any precision whose quarter table fits (window.py:37).
+    int16 [K, nfft] -> int16 [K, nfft].  MFCC's own set (16, 512, 8) runs the stage kernel
+    of the fused path's tables, the others the general kernel with their own curve."""
     stage_id = _lib.STAGE_WINDOW
 
     def __init__(self, width=16, nfft=512, precision=8, _handle=None, device=None):
         if nfft < 8:
             raise ValueError("nfft must be >= 8")                  # window.py:13
-        if (width, nfft, precision) != (16, 512, 8):
-            raise ValueError("CUDA path covers WindowHamming(16, 512, 8) (mfcc.py:47-49)")
+        if nfft & (nfft - 1):
+            raise ValueError("nfft must be a power of two")        # the address slices of window.py:59-66
+        if width != 16:
+            raise ValueError("width must be 16")
+        if not 1 <= precision <= 14:
+            raise ValueError("precision must be 1..14")
         self.width, self.nfft, self.precision = width, nfft, precision
-        self._setup(_handle, device)
+        self._fast = (nfft, precision) == (512, 8)
+        if self._fast:
+            self._setup(_handle, device)
+            return
+        curve = tables.window_curve(nfft, precision)               # raises ValueError like window.py:37
+        self._general_device(device)
+        self._curve = torch.from_numpy(curve.astype("uint16")).to(self.device)
 
     def __call__(self, frames):
         x = self._check(frames, torch.int16, (self.nfft,))
-        return self._run(x, torch.empty_like(x), x.numel() // self.nfft)
+        out = torch.empty_like(x)
+        if self._fast:
+            return self._run(x, out, x.numel() // self.nfft)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_window(
+                C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), x.numel() // self.nfft, self.nfft,
+                self.precision, C.c_void_p(self._curve.data_ptr()),
+                C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class FftStream(_Stage):
-    """FftStream(width=16, nfft=512), mfcc/core/fft_stream.py:6-11.
-    int16 [K, 512] -> int16 [K, 256, 2] (data_r, data_i)."""
+    """FftStream(width=16, nfft=512), mfcc/core/fft_stream.py:6-11, any power-of-two nfft in
+    32..4096.  int16 [K, nfft] -> int16 [K, nfft/2, 2] (data_r, data_i).  nfft = 512 runs the
+    warp-per-frame stage kernel, other sizes the general FFT-core kernel."""
     stage_id = _lib.STAGE_FFT
 
     def __init__(self, width=16, nfft=512, _handle=None, device=None):
         if nfft <= 0 or nfft & (nfft - 1):
-            raise ValueError("Size must be a positive power-of-two integer, not %r" % (nfft,))
-        if (width, nfft) != (16, 512):
-            raise ValueError("CUDA path covers FftStream(16, 512) (mfcc.py:52-53)")
+            raise ValueError("Size must be a positive power-of-two integer, not %r" % (nfft,))   # fft.py:351-353
+        if width != 16:
+            raise ValueError("width must be 16")
+        if nfft < 32:
+            raise ValueError(_HAZARD % nfft)
+        if nfft > 4096:
+            raise ValueError("nfft must be 32..4096")
         self.width, self.nfft = width, nfft
-        self._setup(_handle, device)
+        self._fast = nfft == 512
+        if self._fast:
+            self._setup(_handle, device)
+            return
+        self._general_device(device)
+        self._tw = torch.from_numpy(tables.twiddle_table(nfft, 16).astype("int16")).to(self.device)
 
     def __call__(self, frames):
         x = self._check(frames, torch.int16, (self.nfft,))
         out = torch.empty(x.shape[:-1] + (self.nfft // 2, 2), dtype=torch.int16, device=self.device)
-        return self._run(x, out, x.numel() // self.nfft)
+        if self._fast:
+            return self._run(x, out, x.numel() // self.nfft)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_fft_stream(
+                C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), x.numel() // self.nfft, self.nfft,
+                C.c_void_p(self._tw.data_ptr()), C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class PowerSpectrum(_Stage):
@@ -264,20 +316,40 @@ class Log2Fix(_Stage):
 
 class DCTStream(_Stage):
     """DCTStream(width=16, nfft=16), mfcc/core/dct_stream.py:6-11 (nfft = number of
-    inputs).  int16 [K, nfft] -> int16 [K, nfft]."""
+    inputs), any power-of-two nfft in 8..1024.  int16 [K, nfft] -> int16 [K, nfft].
+    16 and 32 inputs (the sets MFCC builds, mfcc.py:84) run the warp-level stage kernel,
+    other sizes the general FFT-core kernel on the 4*nfft-point transform."""
     stage_id = _lib.STAGE_DCT
 
     def __init__(self, width=16, nfft=16, _handle=None, device=None):
-        if width != 16 or nfft not in (16, 32):
-            raise ValueError("CUDA path covers DCTStream(16, 16|32) (mfcc.py:84)")
+        if width != 16:
+            raise ValueError("width must be 16")
+        if nfft <= 0 or nfft & (nfft - 1):
+            raise ValueError("Size must be a positive power-of-two integer, not %r" % (4 * nfft,))  # fft.py:351-353
+        if nfft < 8:
+            raise ValueError(_HAZARD % (4 * nfft))
+        if nfft > 1024:
+            raise ValueError("nfft must be 8..1024")
         self.width, self.nfft = width, nfft
-        if _handle is not None and _handle.cfg.nfilters != nfft:
-            _handle = None
-        self._setup(_handle, device, nfft)
+        self._fast = nfft in (16, 32)
+        if self._fast:
+            if _handle is not None and _handle.cfg.nfilters != nfft:
+                _handle = None
+            self._setup(_handle, device, nfft)
+            return
+        self._general_device(device)
+        self._tw = torch.from_numpy(tables.twiddle_table(4 * nfft, 16).astype("int16")).to(self.device)
 
     def __call__(self, logs):
         x = self._check(logs, torch.int16, (self.nfft,))
-        return self._run(x, torch.empty_like(x), x.numel() // self.nfft)
+        out = torch.empty_like(x)
+        if self._fast:
+            return self._run(x, out, x.numel() // self.nfft)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_dct_stream(
+                C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), x.numel() // self.nfft, self.nfft,
+                C.c_void_p(self._tw.data_ptr()), C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        return out
 
 
 class Discard:

@@ -205,15 +205,24 @@ def fft_int(xr, xi, size):
     return vr, vi
 
 
-def fft_rtl_banks(xr, xi, size):
+def fft_rtl_banks(xr, xi, size, strict=True):
     """One transform, following FFT + Scheduler of mfcc/misc/fft.py bank by bank and
     cycle by cycle: INIT writes (:438-450), the consume/produce counters and the
     x/y bank multiplexers (:251-308), the twiddle address stepping (:310-316, :331)
     and the 1 + 1 + 7 cycle read/butterfly latency (:140-192, :344).  Reads see a
-    write made in an earlier cycle (nMigen Memory, non-transparent or transparent
-    is irrelevant here: a location is never read in the cycle it is written, which
-    this function asserts).  Returns the `size/2` values read through FFT.o
-    (:426-435, o.addr < size/2 selects mem0)."""
+    write made in an earlier cycle; from 64 points up a location is never read in the
+    cycle it is written, which this function asserts when `strict`, so the transparency of
+    the read ports is irrelevant there.  Returns the `size/2` values read through FFT.o
+    (:426-435, o.addr < size/2 selects mem0).
+
+    A stage lasts size/2 cycles and a butterfly's results land 8 cycles after its read.
+    At 32 points some locations are read in the very cycle they are written: the read
+    ports are nMigen's default transparent ones (:385-393), they return the new value
+    (writes are applied before reads below) and the result is still the transform.  Below
+    32 points the next stage reads locations the previous one has not written yet: a
+    genuine hazard.  With strict=False this model reproduces what the RTL then delivers
+    (tests/golden/rtl_size_vectors.npz, sizes 8 and 16); it is not a Fourier transform,
+    and fft_int() does not follow it there."""
     nb = int(math.log2(size))
     half = size // 2
     mem0 = [(0, 0)] * half
@@ -262,7 +271,7 @@ def fft_rtl_banks(xr, xi, size):
             sel0 = ((tap >> (stage - 1)) & 1) if stage != 0 else 0
             sel1 = stage & 1
             for bank, adr in ((0, a0), (1 if sel1 else 2, a1)):
-                assert last_write_cycle.get((bank, adr), -1) < c, "read/write hazard"
+                assert not strict or last_write_cycle.get((bank, adr), -1) < c, "read/write hazard"
             other = mem1[a1] if sel1 else mem2[a1]
             if sel0:
                 x0, x1 = other, mem0[a0]

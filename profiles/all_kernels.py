@@ -63,5 +63,16 @@ for kw in (dict(), dict(n_mels=40, n_mfcc=13, hop_length=160), dict(center=False
     f1, t = lr(xd[0], taps=True)
     post.to_int16(f1)
     post.scale(f1)
+# general kernels of the stage classes at sizes other than MFCC's
+r = torch.randint(-32768, 32768, (9, 4096), dtype=torch.int16, generator=g).to(dev)
+for nfft in (32, 256, 4096):
+    mfcc_b200.FftStream(16, nfft, device=dev)(r[:, :nfft].contiguous())
+    mfcc_b200.WindowHamming(16, nfft, 7, device=dev)(r[:, :nfft].contiguous())
+for nin in (8, 64, 1024):
+    mfcc_b200.DCTStream(16, nin, device=dev)(r[:, :nin].contiguous())
+mfcc_b200.Frame(16, 400, 160, 512, device=dev)(r[0])
+mfcc_b200.PowerSpectrum(device=dev)(r[:, :512].reshape(9, 256, 2))
+mfcc_b200.Log2Fix(37, 20, device=dev)(r[:, :64].to(torch.int64).abs())
+mfcc_b200.FilterBank(device=dev)(r[:, :256].to(torch.int32).abs())
 torch.cuda.synchronize()
 print("all_kernels.py: all kernels ran")

@@ -396,8 +396,44 @@ def frame_vectors():
     return out
 
 
+def size_vectors():
+    """WindowHamming, FftStream and DCTStream at sizes other than the ones MFCC builds: the
+    stage classes are generic in nfft (window.py:11, fft_stream.py:7, dct_stream.py:7).
+    Random full-range rows, several rows back to back."""
+    with contextlib.redirect_stdout(io.StringIO()):
+        from mfcc.core.fft_stream import FftStream
+        from mfcc.core.dct_stream import DCTStream
+        from mfcc.core.window import WindowHamming
+    rng = np.random.default_rng(23)
+    s16 = lambda v: ((np.asarray(v, dtype=np.int64) + 32768) % 65536) - 32768
+    out = {}
+    for nfft, rows_n in ((8, 4), (16, 4), (64, 3), (256, 2), (1024, 2)):
+        rows = rng.integers(-32768, 32768, (rows_n, nfft))
+        rows[0, : nfft // 2] = 32767
+        rows[0, nfft // 2:] = -32768
+        out["fft%d_in" % nfft] = rows
+        out["fft%d_out" % nfft] = s16(_stream_stage(FftStream(16, nfft), rows, fields_out=("data_r", "data_i")))
+    for nfft, rows_n in ((2, 4), (4, 4), (8, 4), (64, 3), (128, 2)):
+        rows = rng.integers(-32768, 32768, (rows_n, nfft))
+        out["dct%d_in" % nfft] = rows
+        out["dct%d_out" % nfft] = s16(_stream_stage(DCTStream(16, nfft), rows)[:, :, 0])
+    for nfft, prec, rows_n in ((8, 8, 3), (64, 8, 3), (256, 6, 2), (1024, 8, 2), (2048, 10, 2)):
+        rows = rng.integers(-32768, 32768, (rows_n, nfft))
+        rows[1] = 32767
+        with contextlib.redirect_stdout(io.StringIO()):
+            dut = WindowHamming(width=16, nfft=nfft, precision=prec)
+        out["window%d_%d_in" % (nfft, prec)] = rows
+        out["window%d_%d_out" % (nfft, prec)] = s16(_stream_stage(dut, rows)[:, :, 0])
+    return out
+
+
 def main():
     only = sys.argv[1:]
+    if only == ["sizes"]:
+        zv = size_vectors()
+        np.savez_compressed(os.path.join(HERE, "rtl_size_vectors.npz"), **zv)
+        print("size vectors:", {k: v.shape for k, v in zv.items()})
+        return
     if only == ["frames"]:
         fv = frame_vectors()
         np.savez_compressed(os.path.join(HERE, "rtl_frame_vectors.npz"), **fv)
@@ -420,6 +456,9 @@ def main():
         fv = frame_vectors()
         np.savez_compressed(os.path.join(HERE, "rtl_frame_vectors.npz"), **fv)
         print("frame vectors:", {k: v.shape for k, v in fv.items()})
+        zv = size_vectors()
+        np.savez_compressed(os.path.join(HERE, "rtl_size_vectors.npz"), **zv)
+        print("size vectors:", {k: v.shape for k, v in zv.items()})
 
 
 if __name__ == "__main__":

@@ -13,7 +13,7 @@ from oracle import ref_np as R
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = os.path.join(HERE, "golden")
 CASES = sorted(os.path.basename(p)[4:-4] for p in glob.glob(os.path.join(GOLD, "rtl_*.npz"))
-               if not p.endswith(("rtl_stage_vectors.npz", "rtl_frame_vectors.npz")))
+               if not p.endswith(("rtl_stage_vectors.npz", "rtl_frame_vectors.npz", "rtl_size_vectors.npz")))
 
 
 def load(case):
@@ -269,3 +269,109 @@ def test_cuda_frame_and_preemph_match_rtl(fvec):
     pw = mfcc_b200.PowerSpectrum(device="cuda:0")               # class defaults: width 16, 24 bits out
     got = pw(torch.from_numpy(fvec["power24_in"].astype(np.int16)).to("cuda:0")).cpu().numpy()
     assert np.array_equal(got.view(np.uint32).astype(np.int64), fvec["power24_out"])
+
+
+# ---- WindowHamming / FftStream / DCTStream at other sizes (rtl_size_vectors.npz) ----
+FFT_SIZES = (64, 256, 1024)          # 8 and 16: see test_small_fft_hazard_of_the_reference
+DCT_SIZES = (8, 64, 128)
+WINDOW_SETS = ((8, 8), (64, 8), (256, 6), (1024, 8), (2048, 10))
+
+
+@pytest.fixture(scope="module")
+def zvec():
+    return np.load(os.path.join(GOLD, "rtl_size_vectors.npz"))
+
+
+def test_oracle_other_sizes_match_rtl(zvec):
+    for n in FFT_SIZES:
+        re, im = R.fft_stream(zvec["fft%d_in" % n], nfft=n)
+        assert np.array_equal(np.stack([re, im], axis=-1), zvec["fft%d_out" % n]), n
+    for n in DCT_SIZES:
+        assert np.array_equal(R.dct_stream(zvec["dct%d_in" % n], nfft=n), zvec["dct%d_out" % n]), n
+    for n, prec in WINDOW_SETS:
+        got = R.window(zvec["window%d_%d_in" % (n, prec)], nfft=n, precision=prec)
+        assert np.array_equal(got, zvec["window%d_%d_out" % (n, prec)]), (n, prec)
+
+
+def test_small_fft_hazard_of_the_reference(zvec):
+    """Below 32 points the reference's FFT core reads a stage's operands before the previous
+    stage has written them (8-cycle butterfly, size/2 cycles per stage): what comes out is
+    not a transform.  The cycle-level bank model reproduces the RTL there; the operators
+    refuse those sizes instead of imitating the hazard."""
+    for n in (8, 16):
+        x, want = zvec["fft%d_in" % n], zvec["fft%d_out" % n]
+        with pytest.raises(AssertionError):
+            R.fft_rtl_banks(x[1], np.zeros_like(x[1]), n)
+        for r in range(x.shape[0]):
+            re, im = R.fft_rtl_banks(x[r], np.zeros_like(x[r]), n, strict=False)
+            assert np.array_equal(s16(re), want[r, :, 0]) and np.array_equal(s16(im), want[r, :, 1])
+        re, im = R.fft_stream(x, nfft=n)
+        assert not np.array_equal(np.stack([re, im], axis=-1), want)
+    x = zvec["fft64_in"][0]
+    re, im = R.fft_rtl_banks(x, np.zeros_like(x), 64)           # strict: not even a same-cycle access
+    assert np.array_equal(s16(re), zvec["fft64_out"][0, :, 0])
+    x = (np.arange(32) * 2971) % 65536 - 32768                  # 32 points: same-cycle accesses through
+    re, im = R.fft_rtl_banks(x, np.zeros_like(x), 32, strict=False)   # transparent ports, still the transform
+    wr, wi = R.fft_int(x, np.zeros_like(x), 32)
+    assert np.array_equal(re, wr[:16]) and np.array_equal(im, wi[:16])
+
+
+def test_tables_other_sizes():
+    """The curve and twiddles the general kernels are given = the oracle's."""
+    from mfcc_b200 import tables
+    for n, prec in WINDOW_SETS:
+        assert np.array_equal(tables.window_curve(n, prec), R.window_curve(n, prec, 2)[1])
+    for prec in range(1, 15):                                   # window.py:37 holds for every precision:
+        tables.window_curve(64, prec)                           # the quarter table spans 0.46 * 2**(precision+1)
+    for n in (8, 64, 4096):
+        tw = tables.twiddle_table(n, 16)
+        assert tw.shape == (n // 2, 2) and np.abs(tw).max() <= 16384
+        assert all(tuple(tw[k]) == tuple(R.twiddle(n, k)) for k in range(0, n // 2, max(1, n // 16)))
+
+
+@pytest.mark.gpu
+def test_cuda_other_sizes_match_rtl(zvec):
+    import torch
+    import mfcc_b200
+    dev = "cuda:0"
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a).astype(np.int16)).to(dev)
+    for n in FFT_SIZES:
+        got = mfcc_b200.FftStream(16, n, device=dev)(up(zvec["fft%d_in" % n])).cpu().numpy()
+        assert np.array_equal(got, zvec["fft%d_out" % n]), n
+    for n in DCT_SIZES:
+        got = mfcc_b200.DCTStream(16, n, device=dev)(up(zvec["dct%d_in" % n])).cpu().numpy()
+        assert np.array_equal(got, zvec["dct%d_out" % n]), n
+    for n, prec in WINDOW_SETS:
+        got = mfcc_b200.WindowHamming(16, n, prec, device=dev)(up(zvec["window%d_%d_in" % (n, prec)])).cpu().numpy()
+        assert np.array_equal(got, zvec["window%d_%d_out" % (n, prec)]), (n, prec)
+    # the general kernels against the oracle on many random rows, every size they take
+    rng = np.random.default_rng(41)
+    for n in (32, 128, 512, 2048, 4096):
+        x = rng.integers(-32768, 32768, (300, n))
+        re, im = R.fft_stream(x, nfft=n)
+        got = mfcc_b200.FftStream(16, n, device=dev)(up(x)).cpu().numpy()
+        assert np.array_equal(got, np.stack([re, im], axis=-1)), n
+    for n in (8, 16, 32, 256, 1024):
+        x = rng.integers(-32768, 32768, (200, n))
+        got = mfcc_b200.DCTStream(16, n, device=dev)(up(x)).cpu().numpy()
+        assert np.array_equal(got, R.dct_stream(x, nfft=n)), n
+    # 512 / 16 / 32: the specialised stage kernels and the general one agree (C ABI directly)
+    import ctypes as C
+    from mfcc_b200 import _lib, tables
+    x = up(rng.integers(-32768, 32768, (64, 512)))
+    fast = mfcc_b200.FftStream(16, 512, device=dev)(x)
+    tw = up(tables.twiddle_table(512, 16))
+    out = torch.empty_like(fast)
+    _lib.check(_lib.lib().mfcc_b200_fft_stream(C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), 64, 512,
+                                               C.c_void_p(tw.data_ptr()), None))
+    torch.cuda.synchronize()
+    assert torch.equal(out, fast)
+    with pytest.raises(ValueError):
+        mfcc_b200.FftStream(16, 500, device=dev)                # fft.py:351-353
+    for bad in (lambda: mfcc_b200.FftStream(16, 16, device=dev), lambda: mfcc_b200.DCTStream(16, 4, device=dev)):
+        with pytest.raises(ValueError, match="hazard"):
+            bad()
+    with pytest.raises(ValueError):
+        mfcc_b200.WindowHamming(16, 4, 8, device=dev)           # window.py:13
+    with pytest.raises(ValueError):
+        mfcc_b200.WindowHamming(16, 96, 8, device=dev)          # the address slices need a power of two
