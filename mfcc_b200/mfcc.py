@@ -7,6 +7,10 @@ for the ``reset`` signal, and the stage modules reachable as attributes
 mfcc.py:106-114).  ``sink``/``source`` become the argument and the result of
 ``__call__``: int16 samples in, ``[K, nceptrums]`` int16 cepstra out, one row per
 ``last`` of the source stream.
+
+The parameter sets of the reference's tops (nfft 512, 16 or 32 filters) run the fused
+kernel; any other set the reference class accepts (power-of-two nfft 32..4096, 8..1024
+filters, any sample rate) runs the same chain as one general stage kernel per module.
 """
 from __future__ import annotations
 
@@ -55,9 +59,34 @@ class MFCC:
             raise RuntimeError("MFCC needs a CUDA device: there is no CPU fallback")
         self.device = torch.device(device if device is not None else
                                    "cuda:%d" % torch.cuda.current_device())
-        with torch.cuda.device(self.device):
-            self._h = Handle(self.cfg)
         from . import stages as S   # stage operators share the integer-mode handle
+        self._composed = False
+        try:
+            with torch.cuda.device(self.device):
+                self._h = Handle(self.cfg)
+        except (ValueError, _lib.MfccError) as e:
+            # the fused kernels are built for the sets the reference's tops use (nfft 512,
+            # 16 or 32 filters, mel segments of at most 21 / 42 bins); any other set the
+            # reference class accepts runs as the chain of general stage kernels
+            if isinstance(e, _lib.MfccError) and e.code != _lib.EUNSUPPORTED:
+                raise
+            if mode != "int":
+                raise ValueError("fp32 mode covers nfft=512 with 16 or 32 filters (%s)" % e) from None
+            self._h = None
+            self._composed = True
+        if self._composed:
+            self.preemph = S.Preemph(width, device=self.device)
+            self.frame = S.Frame(width, nfft, nfft // 3, nfft, device=self.device)
+            self.window = S.WindowHamming(width, nfft, 8, device=self.device)
+            self.fft_stream = S.FftStream(width, nfft, device=self.device)
+            self.powspec = S.PowerSpectrum(width, 30, device=self.device)
+            self.filterbank = S.FilterBank(30, 16, None, 18, samplerate, nfft, nfilters,
+                                           device=self.device, _general=True)
+            self.log2 = S.Log2Fix(16, 15, device=self.device, _general=True)
+            self.dct_stream = S.DCTStream(width, nfilters, device=self.device)
+            self.discard = S.Discard(width, 0, nceptrums)
+            self._state = None
+            return
         if mode == "int":
             hs = self._h
         else:
@@ -101,6 +130,8 @@ class MFCC:
             out = torch.empty((B, K, nc), dtype=self.out_dtype, device=self.device)
         elif out.shape != (B, K, nc) or out.dtype != self.out_dtype or not out.is_contiguous():
             raise ValueError("out must be a contiguous %s [B, K, nceptrums] tensor" % self.out_dtype)
+        if self._composed:
+            return self._call_composed(x if not single else x[None], K, out, single, taps)
         tp = None
         tensors = None
         if taps:
@@ -128,6 +159,44 @@ class MFCC:
         res = out[0] if single else out
         return (res, tensors) if taps else res
 
+    # ------------------------------------------------------------------ other parameter sets
+    def _chain(self, frames):
+        """frames int16 [..., nfft] -> every later stage, as int16 / int32 tensors."""
+        t = {}
+        t["window"] = self.window(frames)
+        t["fft"] = self.fft_stream(t["window"])
+        t["power"] = self.powspec(t["fft"])
+        mel = self.filterbank(t["power"])                       # int32 holding 16-bit unsigned values
+        lg = self.log2(mel.to(torch.int64))                     # int32, Q4.11
+        t["filter"], t["log"] = mel.to(torch.int16), lg.to(torch.int16)      # same bits, the fused path's dtypes
+        t["dct"] = self.dct_stream(t["log"])
+        return self.discard(t["dct"]), t
+
+    def _call_composed(self, x, K, out, single, taps):
+        """MFCC with constructor arguments the fused kernel is not built for: the chain of
+        mfcc.py:38-104 as one general stage kernel per module (stages.py).  Each row is
+        zero-extended at the INPUT of the chain (software/main.c:135-144), given a leading
+        zero (the reset value of the pre-emphasis register, preemph.py:18-24) and
+        pre-emphasised in one launch over the flattened batch; Frame runs per row."""
+        if taps and x.shape[0] != 1:
+            raise ValueError("taps need a single clip")
+        B, N = x.shape
+        nfft, hop = self.nfft, self.cfg.hop
+        if K == 0:
+            return (out[0] if single else out, {}) if taps else (out[0] if single else out)
+        need = max(N, hop * (K - 1) + nfft)
+        rows = torch.zeros((B, need + 1), dtype=torch.int16, device=self.device)
+        rows[:, 1:N + 1] = x
+        y = self.preemph(rows.reshape(-1)).reshape(B, need + 1)[:, 1:]
+        frames = torch.stack([self.frame(y[b].contiguous(), n_frames=K) for b in range(B)])
+        res, t = self._chain(frames)
+        out.copy_(res)
+        if taps:
+            t = {k: v[0] for k, v in t.items()}
+            t["frame"] = frames[0]
+            return out[0], t
+        return out[0] if single else out
+
     def run_host(self, samples, n_frames=None, out=None):
         """Host buffers in, host buffers out (pinned buffers give full PCIe rate):
         the call a host tool in the place of software/main.c:100-177 makes."""
@@ -144,6 +213,10 @@ class MFCC:
         elif out.shape != (B, K, nc) or out.dtype != self.out_dtype or not out.is_contiguous() \
                 or out.device.type != "cpu":
             raise ValueError("out must be a contiguous CPU %s [B, K, nceptrums] tensor" % self.out_dtype)
+        if self._composed:
+            res = self(x.to(self.device, non_blocking=True), n_frames=K)
+            out.copy_(res.reshape(B, K, nc))
+            return out[0] if single else out
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().mfcc_b200_run_host(
                 self._h.ptr, C.c_void_p(x.data_ptr()), N, N, B, K, C.c_void_p(out.data_ptr()),
@@ -154,6 +227,13 @@ class MFCC:
     def reset(self, n_streams: int = 0):
         """The ``reset`` signal (mfcc.py:28, :116): every stream back to power-on
         state.  With n_streams > 0 allocates the streaming state."""
+        if self._composed:
+            if n_streams:
+                self._state = torch.zeros((n_streams, self.nfft - self.cfg.hop + 1), dtype=torch.int16,
+                                          device=self.device)
+            elif self._state is not None:
+                self._state.zero_()
+            return self
         if n_streams:
             nbytes = C.c_int64()
             _lib.check(_lib.lib().mfcc_b200_state_bytes(self._h.ptr, n_streams, C.byref(nbytes)))
@@ -201,6 +281,14 @@ class MFCC:
             out = torch.empty((S, self.nceptrums), dtype=self.out_dtype, device=self.device)
         elif out.shape != (S, self.nceptrums) or out.dtype != self.out_dtype or not out.is_contiguous():
             raise ValueError("out must be contiguous %s [%d, %d]" % (self.out_dtype, S, self.nceptrums))
+        if self._composed:
+            # state row = the pre-emphasis predecessor and the last nfft - hop samples
+            raw = torch.cat([state, hop.to(self.device)], dim=1)             # [S, nfft + 1]
+            frames = self.preemph(raw.reshape(-1)).reshape(S, self.nfft + 1)[:, 1:].contiguous()
+            state.copy_(raw[:, self.cfg.hop:])
+            res, _t = self._chain(frames)
+            out.copy_(res)
+            return out
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().mfcc_b200_step(
                 self._h.ptr, C.c_void_p(state.data_ptr()), C.c_void_p(hop.data_ptr()), S,

@@ -227,24 +227,29 @@ class FilterBank(_Stage):
     stage_id = _lib.STAGE_MEL
 
     def __init__(self, width=24, width_output=24, width_mul=None, gain=0, sample_rate=16000,
-                 nfft=512, ntap=16, multiplier_cls=None, _handle=None, device=None):
+                 nfft=512, ntap=16, multiplier_cls=None, _handle=None, device=None, _general=False):
         import math
-        from . import tables
         width_mul = width if width_mul is None else width_mul
         self.width, self.width_output, self.width_mul, self.gain = width, width_output, width_mul, gain
         self.sample_rate, self.nfft, self.ntap = sample_rate, nfft, ntap
-        self._fast = (width, width_output, width_mul, gain, nfft) == (30, 16, 30, 18, 512) and ntap in (16, 32)
+        self._fast = (not _general and (width, width_output, width_mul, gain, nfft) == (30, 16, 30, 18, 512)
+                      and ntap in (16, 32))
         if self._fast:
             if _handle is not None and (_handle.cfg.nfilters != ntap or
                                         _handle.cfg.samplerate != sample_rate):
                 _handle = None
-            if _handle is None and torch.cuda.is_available():
-                dev = torch.device(device if device is not None else
-                                   "cuda:%d" % torch.cuda.current_device())
-                with torch.cuda.device(dev):
-                    _handle = Handle(MFCCConfig(samplerate=sample_rate, nfilters=ntap, nceptrums=ntap))
-            self._setup(_handle, device, ntap)
-            return
+            try:
+                if _handle is None and torch.cuda.is_available():
+                    dev = torch.device(device if device is not None else
+                                       "cuda:%d" % torch.cuda.current_device())
+                    with torch.cuda.device(dev):
+                        _handle = Handle(MFCCConfig(samplerate=sample_rate, nfilters=ntap, nceptrums=ntap))
+                self._setup(_handle, device, ntap)
+                return
+            except _lib.MfccError as e:          # a sample rate whose mel segments the warp kernel's table cannot hold
+                if e.code != _lib.EUNSUPPORTED:
+                    raise
+                self._fast = False
         if not (1 <= width <= 31 and 1 <= width_mul <= 31 and 1 <= width_output <= 32 and ntap >= 1):
             raise ValueError("FilterBank: width and width_mul must be <= 31, width_output <= 32")
         if not torch.cuda.is_available():
@@ -283,11 +288,11 @@ class Log2Fix(_Stage):
     kernel (the reference's own bench uses 37 and 20, log.py:143)."""
     stage_id = _lib.STAGE_LOG2
 
-    def __init__(self, width, width_output, multiplier_cls=None, _handle=None, device=None):
+    def __init__(self, width, width_output, multiplier_cls=None, _handle=None, device=None, _general=False):
         import math
         self.width, self.width_output = width, width_output
         self.precision = width_output - math.ceil(math.log2(width)) if width >= 2 else 0     # log.py:114
-        self._fast = (width, width_output) == (16, 15)
+        self._fast = (width, width_output) == (16, 15) and not _general
         if self._fast:
             self._setup(_handle, device)
             return

@@ -39,11 +39,11 @@ with contextlib.redirect_stdout(io.StringIO()):
     from mfcc.core.mfcc import MFCC  # noqa: E402
 
 
-def run_mfcc(samples, n_frames, nfilters, nceptrums, stall=None, seed=0):
+def run_mfcc(samples, n_frames, nfilters, nceptrums, stall=None, seed=0, nfft=512, samplerate=16e3):
     """Drive the reference MFCC top level.  `stall` = probability that the bench
     withholds sink.valid / source.ready in a cycle (exercises the handshakes)."""
     with contextlib.redirect_stdout(io.StringIO()):       # calc_coeffs()/calc_filters() print
-        dut = MFCC(nfft=512, nfilters=nfilters, nceptrums=nceptrums)
+        dut = MFCC(nfft=nfft, samplerate=samplerate, nfilters=nfilters, nceptrums=nceptrums)
         sim = Simulator(dut)
     rng = np.random.default_rng(seed)
     taps = [("window", dut.window.source, "data"), ("fft_r", dut.fft_stream.source, "data_r"),
@@ -427,8 +427,40 @@ def size_vectors():
     return out
 
 
+PARAM_SETS = {      # name: (nfft, samplerate, nfilters, nceptrums, frames)
+    "256_8k_8_8": (256, 8e3, 8, 8, 4),
+    "1024_16k_64_24": (1024, 16e3, 64, 24, 2),
+    "512_44k1_32_13": (512, 44100, 32, 13, 3),
+    "128_16k_16_16": (128, 16e3, 16, 16, 5),
+    "512_16k_8_8": (512, 16e3, 8, 8, 2),
+}
+
+
+def param_vectors():
+    """The reference MFCC top level built with other constructor arguments than its tops
+    use (mfcc/core/mfcc.py:20-21: nfft, samplerate, nfilters and nceptrums are parameters),
+    every stage tapped, on full-scale noise followed by a quiet stretch."""
+    rng = np.random.default_rng(31)
+    out = {}
+    for name, (nfft, sr, nf, nc, nfr) in PARAM_SETS.items():
+        n = nfft + (nfft // 3) * (nfr - 1)
+        x = rng.integers(-32768, 32768, n)
+        x[n // 2:] = rng.integers(-300, 300, n - n // 2)
+        t0 = time.time()
+        taps, cycles = run_mfcc(x, nfr, nf, nc, nfft=nfft, samplerate=sr)
+        out[name + "_samples"] = x.astype(np.int16)
+        for k, v in taps.items():
+            out[name + "_" + k] = v.astype(np.int32)
+        print("%-16s %d frames %7d cycles %.1f s" % (name, nfr, cycles, time.time() - t0))
+    return out
+
+
 def main():
     only = sys.argv[1:]
+    if only == ["params"]:
+        pv = param_vectors()
+        np.savez_compressed(os.path.join(HERE, "rtl_param_vectors.npz"), **pv)
+        return
     if only == ["sizes"]:
         zv = size_vectors()
         np.savez_compressed(os.path.join(HERE, "rtl_size_vectors.npz"), **zv)
@@ -459,6 +491,7 @@ def main():
         zv = size_vectors()
         np.savez_compressed(os.path.join(HERE, "rtl_size_vectors.npz"), **zv)
         print("size vectors:", {k: v.shape for k, v in zv.items()})
+        np.savez_compressed(os.path.join(HERE, "rtl_param_vectors.npz"), **param_vectors())
 
 
 if __name__ == "__main__":

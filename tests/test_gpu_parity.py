@@ -225,9 +225,11 @@ def test_errors(ops):
     with pytest.raises(ValueError):
         m(torch.zeros(1000, dtype=torch.int16))
     with pytest.raises(ValueError):
-        mfcc_b200.MFCC(nfft=256)
+        mfcc_b200.MFCC(nfft=384)                         # not a power of two, fft.py:351-353
     with pytest.raises(ValueError):
-        mfcc_b200.MFCC(nfilters=64, nceptrums=16)
+        mfcc_b200.MFCC(nfilters=64, nceptrums=65)
+    # other sizes construct (chain of general stage kernels, tests/test_rtl_golden.py)
+    assert mfcc_b200.MFCC(nfft=256)._composed and not m._composed
 
 
 @pytest.mark.gpu

@@ -13,7 +13,7 @@ from oracle import ref_np as R
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = os.path.join(HERE, "golden")
 CASES = sorted(os.path.basename(p)[4:-4] for p in glob.glob(os.path.join(GOLD, "rtl_*.npz"))
-               if not p.endswith(("rtl_stage_vectors.npz", "rtl_frame_vectors.npz", "rtl_size_vectors.npz")))
+               if not p.endswith(("rtl_stage_vectors.npz", "rtl_frame_vectors.npz", "rtl_size_vectors.npz", "rtl_param_vectors.npz")))
 
 
 def load(case):
@@ -375,3 +375,77 @@ def test_cuda_other_sizes_match_rtl(zvec):
         mfcc_b200.WindowHamming(16, 4, 8, device=dev)           # window.py:13
     with pytest.raises(ValueError):
         mfcc_b200.WindowHamming(16, 96, 8, device=dev)          # the address slices need a power of two
+
+
+# ---- MFCC with other constructor arguments (rtl_param_vectors.npz) ----
+PARAM_SETS = {"256_8k_8_8": (256, 8e3, 8, 8), "1024_16k_64_24": (1024, 16e3, 64, 24),
+              "512_44k1_32_13": (512, 44100, 32, 13), "128_16k_16_16": (128, 16e3, 16, 16),
+              "512_16k_8_8": (512, 16e3, 8, 8)}
+STAGE_KEYS = ("frame", "window", "fft_r", "fft_i", "power", "filter", "log", "dct")
+
+
+@pytest.fixture(scope="module")
+def pvec():
+    return np.load(os.path.join(GOLD, "rtl_param_vectors.npz"))
+
+
+@pytest.mark.parametrize("name", sorted(PARAM_SETS))
+def test_oracle_other_parameter_sets_match_rtl(pvec, name):
+    nfft, sr, nf, nc = PARAM_SETS[name]
+    K = pvec[name + "_out"].shape[0]
+    out, t = R.mfcc(pvec[name + "_samples"], nfft=nfft, samplerate=sr, nfilters=nf, nceptrums=nc,
+                    n_frames=K, taps=True)
+    for k in STAGE_KEYS:
+        assert np.array_equal(s16(t[k]), s16(pvec[name + "_" + k])), k
+    assert np.array_equal(out, s16(pvec[name + "_out"]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(PARAM_SETS))
+def test_cuda_other_parameter_sets_match_rtl(pvec, name):
+    """MFCC(...) with arguments the fused kernel is not built for runs the chain of general
+    stage kernels: every stage against the RTL, batch against the oracle, streaming against
+    batch."""
+    import torch
+    import mfcc_b200
+    nfft, sr, nf, nc = PARAM_SETS[name]
+    hop = nfft // 3
+    dev = "cuda:0"
+    op = mfcc_b200.MFCC(nfft=nfft, samplerate=sr, nfilters=nf, nceptrums=nc, device=dev)
+    x = pvec[name + "_samples"]
+    K = pvec[name + "_out"].shape[0]
+    xd = torch.from_numpy(x).to(dev)
+    out, t = op(xd, n_frames=K, taps=True)
+    got = {k: v.cpu().numpy() for k, v in t.items()}
+    got["fft_r"], got["fft_i"] = got["fft"][..., 0], got["fft"][..., 1]
+    for k in STAGE_KEYS:
+        assert np.array_equal(s16(got[k]), s16(pvec[name + "_" + k])), k
+    assert np.array_equal(out.cpu().numpy(), s16(pvec[name + "_out"]))
+    # a ragged batch, zero-extended rows, host buffers
+    rng = np.random.default_rng(3)
+    xb = rng.integers(-32768, 32768, (3, nfft + hop * 6 + 5)).astype(np.int16)
+    want = np.stack([R.mfcc(r, nfft=nfft, samplerate=sr, nfilters=nf, nceptrums=nc, n_frames=9) for r in xb])
+    assert np.array_equal(op(torch.from_numpy(xb).to(dev), n_frames=9).cpu().numpy(), want)
+    assert np.array_equal(op.run_host(torch.from_numpy(xb), n_frames=9).numpy(), want)
+    assert op(torch.from_numpy(xb).to(dev)).shape == (3, 7, nc)
+    # streaming: hop by hop from reset = the batch path on the stream with nfft - hop zeros in front
+    op.reset(3)
+    lead = np.zeros((3, nfft - hop), dtype=np.int16)
+    full = np.concatenate([lead, xb[:, :hop * 5]], axis=1)
+    wb = np.stack([R.mfcc(r, nfft=nfft, samplerate=sr, nfilters=nf, nceptrums=nc) for r in full])
+    for j in range(5):
+        col = op.step(torch.from_numpy(np.ascontiguousarray(xb[:, hop * j:hop * (j + 1)])).to(dev))
+        assert np.array_equal(col.cpu().numpy(), wb[:, j]), j
+
+
+@pytest.mark.gpu
+def test_cuda_parameter_limits():
+    import mfcc_b200
+    with pytest.raises(ValueError, match="hazard"):
+        mfcc_b200.MFCC(nfft=16, nfilters=8, nceptrums=8, device="cuda:0")
+    with pytest.raises(ValueError, match="hazard"):
+        mfcc_b200.MFCC(nfft=256, nfilters=4, nceptrums=4, device="cuda:0")
+    with pytest.raises(ValueError):
+        mfcc_b200.MFCC(nfft=500, device="cuda:0")                 # fft.py:351-353
+    with pytest.raises(ValueError):
+        mfcc_b200.MFCC(nfft=256, mode="fp32", device="cuda:0")
