@@ -45,6 +45,36 @@ __global__ void k(int *out, int a0, int b0)
                 else if ((i & 3) == 2) asm volatile("shr.s32 %0, %0, %1;" : "+r"(v[i]) : "r"(b + rep));
                 else asm volatile("add.s32 %0, %0, %1;" : "+r"(v[i]) : "r"(v[(i + 3) % CH]));
             }
+            if (OP == 11) asm volatile("mad.lo.s32 %0, %0, 11585, %1;" : "+r"(v[i]) : "r"(it));       // IMAD R, R, imm, R
+            if (OP == 12) asm volatile("mad.lo.s32 %0, %0, %1, 16382;" : "+r"(v[i]) : "r"(b));        // IMAD R, R, R, imm
+            if (OP == 13) {  // 1:1 IMAD-imm : SHF
+                if (i & 1) asm volatile("mad.lo.s32 %0, %0, 11585, %1;" : "+r"(v[i]) : "r"(it));
+                else       asm volatile("shr.s32 %0, %0, %1;" : "+r"(v[i]) : "r"(b + rep));
+            }
+            if (OP == 14) {  // 2:1 IMAD-imm : SHF
+                if ((i % 3) < 2) asm volatile("mad.lo.s32 %0, %0, 11585, %1;" : "+r"(v[i]) : "r"(it));
+                else             asm volatile("shr.s32 %0, %0, %1;" : "+r"(v[i]) : "r"(b + rep));
+            }
+            if (OP == 15) asm volatile("shf.r.clamp.b32 %0, %0, %1, 1;" : "+r"(v[i]) : "r"(b));        // SHF with an immediate count
+            if (OP == 16) {  // float pipe for comparison: FFMA 3-register form
+                float f = __int_as_float(v[i]);
+                asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f) : "f"(__int_as_float(b)), "f"(__int_as_float(it)));
+                v[i] = __float_as_int(f);
+            }
+            if (OP == 17) {  // FFMA with an immediate multiplier
+                float f = __int_as_float(v[i]);
+                asm volatile("fma.rn.f32 %0, %0, 0f3F800100, %1;" : "+f"(f) : "f"(__int_as_float(it)));
+                v[i] = __float_as_int(f);
+            }
+            if (OP == 18) {  // 1:1:1 IMAD : SHF : FFMA (three pipes?)
+                if (i % 3 == 0) asm volatile("mad.lo.s32 %0, %0, %1, %2;" : "+r"(v[i]) : "r"(b), "r"(it));
+                else if (i % 3 == 1) asm volatile("shr.s32 %0, %0, %1;" : "+r"(v[i]) : "r"(b + rep));
+                else {
+                    float f = __int_as_float(v[i]);
+                    asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f) : "f"(__int_as_float(b)), "f"(__int_as_float(it)));
+                    v[i] = __float_as_int(f);
+                }
+            }
         }
       }
     }
@@ -92,5 +122,13 @@ int main()
     run<8>("SHF.L funnel", s, clk, 1);
     run<9>("shl+add (LEA?)", s, clk, 1);
     run<10>("IMAD:SHF:IADD 2:1:1", s, clk, 1);
+    run<11>("IMAD R,R,imm,R", s, clk, 1);
+    run<12>("IMAD R,R,R,imm", s, clk, 1);
+    run<13>("IMAD-imm+SHF 1:1", s, clk, 1);
+    run<14>("IMAD-imm:SHF 2:1", s, clk, 1);
+    run<15>("SHF imm count", s, clk, 1);
+    run<16>("FFMA 3-reg", s, clk, 1);
+    run<17>("FFMA imm", s, clk, 1);
+    run<18>("IMAD:SHF:FFMA 1:1:1", s, clk, 1);
     return 0;
 }
