@@ -22,9 +22,10 @@ def main():
     lib = sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "mfcc_b200", "libmfcc_b200.so")
     with tempfile.TemporaryDirectory() as td:
         subprocess.check_call(["cuobjdump", "-xelf", "all", lib], cwd=td, stdout=subprocess.DEVNULL)
-        cub = [f for f in os.listdir(td) if f.endswith(".cubin")][0]
-        dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(td, cub)], capture_output=True,
-                             text=True).stdout
+        dis = ""
+        for cub in sorted(f for f in os.listdir(td) if f.endswith(".cubin")):
+            dis += subprocess.run(["nvdisasm", "-g", "-c", os.path.join(td, cub)], capture_output=True,
+                                  text=True).stdout
     sec, cur = None, None
     per_line = collections.Counter()
     per_op = collections.defaultdict(collections.Counter)
