@@ -24,7 +24,7 @@ constexpr unsigned FULL = 0xffffffffu;
 struct alignas(16) DevTables {
     int2     twB[128];       // stages 4..7, doubled (2re, 2im): [16 | 16 | 32 | 64] entries
     int2     tw8[256];       // stage 8, doubled, natural order
-    uint2    melab[672];     // FilterBank weights, padded per segment: see mel_warp()
+    uint2    melab[704];     // FilterBank weights, padded per segment: see mel_warp()
     uint32_t pad0[4];
     uint16_t logfrac[2048];  // Log2Fix fraction bits 10..1 for every 12-bit mantissa: see log2fix_tab()
     int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
@@ -36,6 +36,7 @@ struct alignas(16) DevTables {
     uint16_t paddr[256];     // word address of bin b in the padded power layout: every segment
                              // starts in a bank no other segment start uses, so the 32 lanes of
                              // mel_warp() read 32 different banks at every step
+    uint4    pstore[2 * 32]; // [i / 4][lane]: paddr[lane + 32 i], i = 0..7: where the lane's power values go
     int32_t  mel_lo_bit;     // filterbank.py:122
     int32_t  nseg;
     int32_t  pad[2];
@@ -230,13 +231,14 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int b = lane + 32 * i;
-        const unsigned u0 = xbuf[b], u1 = xbuf[272 + b];
         const int2 w = tab->tw8[b];
+        const unsigned u0 = xbuf[b], u1 = xbuf[272 + b];
         const int x1r = lo16(u1), x1i = hi16(u1);
+        const int x0r = lo16(u0), x0i = hi16(u0);
         unsigned qr = (unsigned)(x1r * w.x) - (unsigned)(x1i * w.y) + 16382u;
         unsigned qi = (unsigned)(x1i * w.x) + (unsigned)(x1r * w.y) + 16382u;
-        re[i] = (int)(((unsigned)lo16(u0) << 15) + qr) >> 16;
-        im[i] = (int)(((unsigned)hi16(u0) << 15) + qi) >> 16;
+        re[i] = (int)(((unsigned)x0r << 15) + qr) >> 16;
+        im[i] = (int)(((unsigned)x0i << 15) + qi) >> 16;
     }
     __syncwarp();   // xbuf may be reused by the caller
 }
@@ -254,7 +256,9 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
 //     Bbar_g = sum d * wb,  wb = 2^30 - w on non-closing bins, 0 on the closing bin
 // so lane g-1 walks segment g once with two 64-bit multiply-adds per bin and takes
 // Abar_{g-1} from its neighbour.  melab[j * NF + lane] = (wa, wb) of the j-th bin of the
-// lane's segment, zero past its end: every lane runs the same MAXSEG steps, no branches.
+// lane's segment, zero past its end: every lane runs the same MAXSEG steps, no branches
+// (32 filters: the weights of steps 2jj, 2jj+1 sit side by side, melab[(jj * NF + lane) * 2 + {0, 1}],
+// one 128-bit load per two steps, 22 steps).
 template <int NF>
 __device__ __forceinline__ unsigned mel_warp(const unsigned *pw, const DevTables *tab, int lane)
 {
@@ -263,12 +267,16 @@ __device__ __forceinline__ unsigned mel_warp(const unsigned *pw, const DevTables
     const unsigned *p = pw + tab->seg_walk[li];
     unsigned long long a = 0, b = 0;
     if (NF == 32) {
+        // two steps per 128-bit weight load: melab as uint4 [step / 2][lane]
+        const uint4 *wt = reinterpret_cast<const uint4 *>(tab->melab) + li;
 #pragma unroll
-        for (int j = 0; j < MAXSEG; ++j) {
-            const unsigned d = p[j];
-            const uint2 w = tab->melab[j * NF + li];
-            a += (unsigned long long)d * w.x;
-            b += (unsigned long long)d * w.y;
+        for (int jj = 0; jj < (MAXSEG + 1) / 2; ++jj) {
+            const unsigned d0 = p[2 * jj], d1 = p[2 * jj + 1];
+            const uint4 w = wt[jj * NF];
+            a += (unsigned long long)d0 * w.x;
+            b += (unsigned long long)d0 * w.y;
+            a += (unsigned long long)d1 * w.z;
+            b += (unsigned long long)d1 * w.w;
         }
     } else {
         // 16 filters: the two half-warps split the steps of each segment

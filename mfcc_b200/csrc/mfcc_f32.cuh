@@ -21,6 +21,7 @@ constexpr int XWF = 1040;              // 32-bit words of the per-warp exchange 
 constexpr int T1_STRIDE = 36;          // float2 per row of the first transpose
 constexpr int PW_OFF = 576;            // power spectrum lives behind the transpose area
 constexpr int PW_WORDS = XWF - PW_OFF; // padded power-spectrum area: see DevTablesF::paddr
+constexpr int MEL_J0 = 7;              // 32 filters: segments 1..16 have at most 7 bins (checked by create)
 constexpr unsigned FULL = 0xffffffffu;
 
 struct alignas(16) DevTablesF {
@@ -33,7 +34,8 @@ struct alignas(16) DevTablesF {
     uint16_t paddr[264];               // word address of bin b in the padded power area
     uint16_t seg_base[32];             // address of the first bin of lane's segment (segment lane+1)
     float  mel_floor;                  // energies are clamped to this before log2 (0 = off)
-    int32_t pad[3];
+    int32_t mel_tail_lane;             // lanes below this have no bins at steps >= MEL_J0 (32 filters): 16, or 0
+    int32_t pad[2];
 };
 static_assert(sizeof(DevTablesF) % 16 == 0, "DevTablesF must be int4-copyable");
 
@@ -183,11 +185,22 @@ __device__ __forceinline__ float cepstrum_warp_f32(float *pw, float *lbuf, const
     float u = 0.0f, v = 0.0f;
     if (NF == 32) {
 #pragma unroll
-        for (int j = 0; j < MAXSEG; ++j) {
+        for (int j = 0; j < MEL_J0; ++j) {
             const float d = p[j];
             const float2 w = tab->melw[j * NF + li];
             u = fmaf(d, w.x, u);
             v = fmaf(d, w.y, v);
+        }
+        // only the long segments of the upper filters go on: with the lower half-warp
+        // predicated off a 64-bit weight load is one shared-memory wavefront, not two
+        if (lane >= tab->mel_tail_lane) {
+#pragma unroll
+            for (int j = MEL_J0; j < MAXSEG; ++j) {
+                const float d = p[j];
+                const float2 w = tab->melw[j * NF + li];
+                u = fmaf(d, w.x, u);
+                v = fmaf(d, w.y, v);
+            }
         }
     } else {
         const int j0 = (lane >> 4) * (MAXSEG / 2);

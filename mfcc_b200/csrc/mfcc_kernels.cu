@@ -87,10 +87,11 @@ struct Tile {
     int nf, len, lo, hi;     // frames, samples needed in raw[], TMA covers raw[lo, hi)
 };
 
-__device__ __forceinline__ Tile tile_geo(const RunParams &p, long long t) {
+// tile `ti` of clip `ci` (the persistent kernels step (ci, ti) by the grid size without dividing)
+__device__ __forceinline__ Tile tile_geo(const RunParams &p, long long ci, int ti) {
     Tile g;
-    g.ci = t / p.tiles_per_clip;
-    g.f0 = (t - g.ci * p.tiles_per_clip) * FT;
+    g.ci = ci;
+    g.f0 = (long long)ti * FT;
     long long left = p.n_frames - g.f0;
     g.nf = left < FT ? (int)left : FT;
     g.clip = p.x + g.ci * p.clip_stride;
@@ -105,6 +106,26 @@ __device__ __forceinline__ Tile tile_geo(const RunParams &p, long long t) {
     g.hi = (int)(hi - g.a0);
     return g;
 }
+
+// position of a persistent CTA in the tile sequence: tile = ci * tiles_per_clip + ti
+struct TileIter {
+    long long tile, ci;
+    int ti, dq, dr, tpc;
+    __device__ __forceinline__ void init(const RunParams &p) {
+        tpc = p.tiles_per_clip;
+        tile = blockIdx.x;
+        ci = (int)(blockIdx.x / (unsigned)tpc);
+        ti = (int)(blockIdx.x % (unsigned)tpc);
+        dq = (int)(gridDim.x / (unsigned)tpc);
+        dr = (int)(gridDim.x % (unsigned)tpc);
+    }
+    __device__ __forceinline__ void next() {
+        tile += gridDim.x;
+        ci += dq;
+        ti += dr;
+        if (ti >= tpc) { ti -= tpc; ++ci; }
+    }
+};
 
 // ------------------------------------------------------------------ one frame by one warp
 // pre: pre-emphasised samples of the frame in shared memory (even halfword offset).
@@ -126,11 +147,14 @@ __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, c
     int re[8], im[8];
     fft512_warp(xr, xbuf, tab, lane, re, im);
     // PowerSpectrum: top 30 bits of the 32-bit sum   pow2.py:32, :64
+    // where the lane's eight power values go in the padded layout: two 128-bit loads
+    const uint4 pa0 = tab->pstore[lane], pa1 = tab->pstore[32 + lane];
+    const unsigned pst[8] = {pa0.x, pa0.y, pa0.z, pa0.w, pa1.x, pa1.y, pa1.z, pa1.w};
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int b = lane + 32 * i;
         const unsigned pw = ((unsigned)(re[i] * re[i]) + (unsigned)(im[i] * im[i])) >> 2;
-        xbuf[tab->paddr[b]] = pw;
+        xbuf[pst[i]] = pw;
         if (TAPS && tp.d_fft) { tp.d_fft[(k * NBINS + b) * 2] = (int16_t)re[i]; tp.d_fft[(k * NBINS + b) * 2 + 1] = (int16_t)im[i]; }
         if (TAPS && tp.d_power) tp.d_power[k * NBINS + b] = pw;
     }
@@ -156,8 +180,8 @@ struct Smem {
     alignas(8) uint64_t mbar;
 };
 
-__device__ __forceinline__ void issue_tile(const RunParams &p, long long t, Smem *sm) {
-    const Tile g = tile_geo(p, t);
+__device__ __forceinline__ void issue_tile(const RunParams &p, const TileIter &it, Smem *sm) {
+    const Tile g = tile_geo(p, it.ci, it.ti);
     const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
     if (bytes) {
         mbar_arrive_expect_tx(&sm->mbar, bytes);
@@ -182,12 +206,14 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
     if (tid == 0) mbar_init(&sm->mbar, 1);
     __syncthreads();
 
-    long long tile = blockIdx.x;
-    if (tid == 0 && tile < p.n_tiles) issue_tile(p, tile, sm);
+    TileIter it;
+    it.init(p);
+    if (tid == 0 && it.tile < p.n_tiles) issue_tile(p, it, sm);
     uint32_t phase = 0;
 
-    for (; tile < p.n_tiles; tile += gridDim.x) {
-        const Tile g = tile_geo(p, tile);
+    while (it.tile < p.n_tiles) {
+        const Tile g = tile_geo(p, it.ci, it.ti);
+        it.next();
         // samples the bulk copy does not cover: before the clip (zeros), the ragged
         // tail and everything past the end (zeros, software/main.c:135-144)
         for (int j = tid; j < g.lo; j += THREADS) sm->raw[j] = 0;
@@ -200,31 +226,37 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
         __syncthreads();
 
         // Preemph, once per sample: y = x + (prev >> 5) - prev, 16-bit   preemph.py:18-28
+        // eight samples (one 128-bit word) per thread and step; whatever lies between
+        // g.len and the end of the last word is never read back
         {
+            const uint4 *r128 = reinterpret_cast<const uint4 *>(sm->raw);
             const unsigned *r32 = reinterpret_cast<const unsigned *>(sm->raw);
-            unsigned *p32 = reinterpret_cast<unsigned *>(sm->pre);
-            const int nw = (g.len + 1) >> 1;
-            for (int i = tid; i < nw; i += THREADS) {
-                const unsigned w1 = r32[i];
-                const int sp = i ? hi16(r32[i - 1]) : 0;
-                const int s0 = lo16(w1), s1 = hi16(w1);
-                const int y0 = s0 + (sp >> 5) - sp;
-                const int y1 = s1 + (s0 >> 5) - s0;
-                p32[i] = __byte_perm((unsigned)y0, (unsigned)y1, 0x5410);
+            uint4 *p128 = reinterpret_cast<uint4 *>(sm->pre);
+            const int nq = (g.len + 7) >> 3;
+            for (int i = tid; i < nq; i += THREADS) {
+                const uint4 w = r128[i];
+                int sp = i ? hi16(r32[4 * i - 1]) : 0;
+                const unsigned ws[4] = {w.x, w.y, w.z, w.w};
+                unsigned o[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int s0 = lo16(ws[q]), s1 = hi16(ws[q]);
+                    const int y0 = s0 + (sp >> 5) - sp;
+                    const int y1 = s1 + (s0 >> 5) - s0;
+                    o[q] = __byte_perm((unsigned)y0, (unsigned)y1, 0x5410);
+                    sp = s1;
+                }
+                p128[i] = make_uint4(o[0], o[1], o[2], o[3]);
             }
         }
         __syncthreads();
-        {   // raw[] is free again: prefetch the next tile while this one is computed
-            const long long nxt = tile + gridDim.x;
-            if (tid == 0 && nxt < p.n_tiles) issue_tile(p, nxt, sm);
-        }
+        // raw[] is free again: prefetch the next tile while this one is computed
+        if (tid == 0 && it.tile < p.n_tiles) issue_tile(p, it, sm);
         const int off0 = (int)(HOP * g.f0 - g.a0);          // even, 8..14
-        int16_t *orow = static_cast<int16_t *>(p.out) + g.ci * p.out_clip_stride;
-        for (int fl = warp; fl < g.nf; fl += WARPS) {
-            const long long k = g.f0 + fl;
+        int16_t *otile = static_cast<int16_t *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
+        for (int fl = warp; fl < g.nf; fl += WARPS)
             frame_warp<NF, TAPS>(sm->pre + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
-                           orow + k * p.nceptrums, p.nceptrums, p.taps, k);
-        }
+                                 otile + fl * p.nceptrums, p.nceptrums, p.taps, g.f0 + fl);
         __syncthreads();
     }
 }
@@ -241,8 +273,8 @@ struct SmemF {
     alignas(8) uint64_t mbar[2];
 };
 
-__device__ __forceinline__ void issue_tile_f(const RunParams &p, long long t, SmemF *sm, int buf) {
-    const Tile g = tile_geo(p, t);
+__device__ __forceinline__ void issue_tile_f(const RunParams &p, const TileIter &it, SmemF *sm, int buf) {
+    const Tile g = tile_geo(p, it.ci, it.ti);
     const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
     if (bytes) {
         mbar_arrive_expect_tx(&sm->mbar[buf], bytes);
@@ -270,30 +302,29 @@ __global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
     if (tid == 0) { mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1); }
     __syncthreads();
 
-    long long tile = blockIdx.x;
-    if (tid == 0 && tile < p.n_tiles) issue_tile_f(p, tile, sm, 0);
-    for (int it = 0; tile < p.n_tiles; tile += gridDim.x, ++it) {
+    TileIter ti;
+    ti.init(p);
+    if (tid == 0 && ti.tile < p.n_tiles) issue_tile_f(p, ti, sm, 0);
+    for (int it = 0; ti.tile < p.n_tiles; ++it) {
         const int buf = it & 1;
-        const Tile g = tile_geo(p, tile);
+        const Tile g = tile_geo(p, ti.ci, ti.ti);
+        ti.next();
         int16_t *raw = sm->raw[buf];
         for (int j = tid; j < g.lo; j += THREADS) raw[j] = 0;
         for (int j = g.hi + tid; j < g.len; j += THREADS) {
             const long long s = g.a0 + j;
             raw[j] = (s >= 0 && s < p.n_samples) ? g.clip[s] : (int16_t)0;
         }
-        {   // the other buffer was released by the barrier that ended the previous tile
-            const long long nxt = tile + gridDim.x;
-            if (tid == 0 && nxt < p.n_tiles) issue_tile_f(p, nxt, sm, buf ^ 1);
-        }
+        // the other buffer was released by the barrier that ended the previous tile
+        if (tid == 0 && ti.tile < p.n_tiles) issue_tile_f(p, ti, sm, buf ^ 1);
         mbar_wait(&sm->mbar[buf], (uint32_t)(it >> 1) & 1u);
         __syncthreads();
         const int off0 = (int)(HOP * g.f0 - g.a0);          // even, 8..14
-        float *orow = static_cast<float *>(p.out) + g.ci * p.out_clip_stride;
+        float *otile = static_cast<float *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
         for (int fl = warp; fl < g.nf; fl += WARPS) {
-            const long long k = g.f0 + fl;
             mfccf::power_warp_f32(raw + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane);
             const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, sm->xbuf[warp], &sm->tab, lane);
-            if (lane < p.nceptrums) orow[k * p.nceptrums + lane] = c;
+            if (lane < p.nceptrums) otile[fl * p.nceptrums + lane] = c;
             __syncwarp();
         }
         __syncthreads();
@@ -598,7 +629,9 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
                 const bool closing = (first + j == b);
                 const uint32_t w = c.mel_weight[first + j];
                 const uint32_t wa = closing ? (1u << 30) : w, wb = closing ? 0u : (1u << 30) - w;
-                t.melab[(j0 + j) * c.nfilters + lane_of] = g == 0 ? make_uint2(0u, wa) : make_uint2(wa, wb);
+                const int st = j0 + j;
+                const int at = c.nfilters == 32 ? ((st >> 1) * 32 + lane_of) * 2 + (st & 1) : st * c.nfilters + lane_of;
+                t.melab[at] = g == 0 ? make_uint2(0u, wa) : make_uint2(wa, wb);
             }
             first = b + 1;
             ++g;
@@ -606,7 +639,13 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
     }
     if (g != c.nfilters + 1 || first != NBINS)
         return fail(MFCC_B200_EUNSUPPORTED, "mel tables must describe nfilters+1 segments ending at the last bin");
-    if (pad_next + maxseg > XW) return fail(MFCC_B200_EUNSUPPORTED, "padded power layout does not fit the exchange buffer");
+    for (int l = 0; l < 32; ++l) {
+        uint32_t ps[8];
+        for (int i = 0; i < 8; ++i) ps[i] = t.paddr[l + 32 * i];
+        t.pstore[l] = make_uint4(ps[0], ps[1], ps[2], ps[3]);
+        t.pstore[32 + l] = make_uint4(ps[4], ps[5], ps[6], ps[7]);
+    }
+    if (pad_next + maxseg + 1 > XW) return fail(MFCC_B200_EUNSUPPORTED, "padded power layout does not fit the exchange buffer");
     for (int z = 0; z < 2048; ++z) t.logfrac[z] = (uint16_t)log2fix_frac(2048u + z);
     t.nseg = g;
     t.mel_lo_bit = c.mel_lo_bit;
@@ -690,6 +729,12 @@ int build_tables_f(const mfcc_b200_cfg &c, mfccf::DevTablesF &t) {
         else t.melw[((g == 1 ? len[0] : 0) + j) * nf + (g - 1)] = make_float2(rise, fall);
     }
     t.mel_floor = c.f_mel_floor > 0.0f ? c.f_mel_floor : 0.0f;
+    // the kernel's mel walk drops the lower half-warp after MEL_J0 steps when it has nothing left
+    t.mel_tail_lane = 16;
+    if (nf == 32)
+        for (int j = mfccf::MEL_J0; j < maxseg; ++j)
+            for (int l = 0; l < 16; ++l)
+                if (t.melw[j * nf + l].x != 0.0f || t.melw[j * nf + l].y != 0.0f) t.mel_tail_lane = 0;
     return MFCC_B200_OK;
 }
 

@@ -19,7 +19,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def main():
     pat = sys.argv[1]
-    lib = sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "mfcc_b200", "libmfcc_b200.so")
+    lib = os.path.abspath(sys.argv[2]) if len(sys.argv) > 2 else os.path.join(ROOT, "mfcc_b200", "libmfcc_b200.so")
     with tempfile.TemporaryDirectory() as td:
         subprocess.check_call(["cuobjdump", "-xelf", "all", lib], cwd=td, stdout=subprocess.DEVNULL)
         dis = ""
