@@ -29,6 +29,21 @@ constexpr int THREADS = WARPS * 32;
 constexpr int FT      = 24;                                        // frames per tile
 constexpr int RAWN    = ((HOP * (FT - 1) + NFFT + 15) + 7) & ~7;   // samples per tile buffer
 constexpr int CTAS_PER_SM = 4;
+// the fp32 kernel has its own CTA shape (it is bound by shared-memory latency, not by issue)
+#ifndef MFCC_F32_WARPS
+#define MFCC_F32_WARPS 8
+#endif
+#ifndef MFCC_F32_FT
+#define MFCC_F32_FT 24
+#endif
+constexpr int WARPS_F   = MFCC_F32_WARPS;
+constexpr int THREADS_F = WARPS_F * 32;
+constexpr int FT_F      = MFCC_F32_FT;
+constexpr int RAWN_F    = ((HOP * (FT_F - 1) + NFFT + 15) + 7) & ~7;
+#ifndef MFCC_F32_CTAS
+#define MFCC_F32_CTAS 3
+#endif
+constexpr int CTAS_PER_SM_F = MFCC_F32_CTAS;
 
 struct RunParams {
     const int16_t *x;
@@ -74,9 +89,9 @@ __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t
 }
 
 // sign-extending 16-bit shared load (SASS LDS.S16; plain C++ compiles to LDS.U16 + PRMT)
-__device__ __forceinline__ int lds_s16(const int16_t *p) {
+__device__ __forceinline__ int lds_s16(uint32_t saddr) {
     int v;
-    asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)));
+    asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(saddr));
     return v;
 }
 
@@ -87,23 +102,28 @@ struct Tile {
     int nf, len, lo, hi;     // frames, samples needed in raw[], TMA covers raw[lo, hi)
 };
 
-// tile `ti` of clip `ci` (the persistent kernels step (ci, ti) by the grid size without dividing)
+// tile `ti` of clip `ci` (the persistent kernels step (ci, ti) by the grid size without dividing).
+// A tile starts FT * HOP samples after the previous one, a multiple of 8: raw[0] is always the
+// sample 8 before the tile's first frame, so every bulk copy is 16-byte aligned on both sides.
+static_assert((FT * HOP) % 8 == 0 && (FT_F * HOP) % 8 == 0, "tiles must start on 16-byte boundaries of the clip");
+constexpr int OFF0 = 8;                                      // raw[OFF0] = first sample of the tile's first frame
+template <int FTT = FT>
 __device__ __forceinline__ Tile tile_geo(const RunParams &p, long long ci, int ti) {
     Tile g;
     g.ci = ci;
-    g.f0 = (long long)ti * FT;
-    long long left = p.n_frames - g.f0;
-    g.nf = left < FT ? (int)left : FT;
-    g.clip = p.x + g.ci * p.clip_stride;
-    g.a0 = ((HOP * g.f0) & ~7LL) - 8;                       // <= HOP*f0 - 1: the predecessor sample
-    g.len = (int)(HOP * (g.f0 + g.nf - 1) + NFFT - g.a0);   // <= RAWN
-    long long lo = g.a0 < 0 ? 0 : g.a0;
-    long long hi = g.a0 + ((g.len + 7) & ~7);
-    long long lim = p.n_samples & ~7LL;
-    if (hi > lim) hi = lim;
-    if (!p.aligned || hi < lo) hi = lo;
-    g.lo = (int)(lo - g.a0);
-    g.hi = (int)(hi - g.a0);
+    g.f0 = (long long)ti * FTT;
+    const long long left = p.n_frames - g.f0;
+    g.nf = left < FTT ? (int)left : FTT;
+    g.clip = p.x + ci * p.clip_stride;
+    g.a0 = (long long)ti * (FTT * HOP) - OFF0;                // < 0 only for the first tile: the predecessor is 0
+    g.len = HOP * (g.nf - 1) + NFFT + OFF0;                  // <= RAWN
+    g.lo = ti == 0 ? OFF0 : 0;
+    // the bulk copy moves whole 16-byte words that lie inside the clip
+    const long long room = (p.n_samples & ~7LL) - g.a0;
+    int hi = (g.len + 7) & ~7;
+    if (room < hi) hi = room < g.lo ? g.lo : (int)room;
+    if (!p.aligned) hi = g.lo;
+    g.hi = hi;
     return g;
 }
 
@@ -137,11 +157,12 @@ __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, c
 {
     // WindowHamming: top 16 bits of signed16 * unsigned9 = (y * curve) >> 9   window.py:74-75,84
     const int bt = (int)(__brev((unsigned)lane) >> 27);
+    const uint32_t pre_s = smem_u32(pre + bt);
     int xr[16];
 #pragma unroll
     for (int l = 0; l < 16; ++l) {
         const int n = bt + 32 * brev4(l);
-        xr[l] = (lds_s16(pre + n) * (int)tab->curve[n]) >> 9;
+        xr[l] = (lds_s16(pre_s + 64u * brev4(l)) * (int)tab->curve[n]) >> 9;
         if (TAPS && tp.d_window) tp.d_window[k * NFFT + n] = (int16_t)xr[l];
     }
     int re[8], im[8];
@@ -252,10 +273,9 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
         __syncthreads();
         // raw[] is free again: prefetch the next tile while this one is computed
         if (tid == 0 && it.tile < p.n_tiles) issue_tile(p, it, sm);
-        const int off0 = (int)(HOP * g.f0 - g.a0);          // even, 8..14
         int16_t *otile = static_cast<int16_t *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
         for (int fl = warp; fl < g.nf; fl += WARPS)
-            frame_warp<NF, TAPS>(sm->pre + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
+            frame_warp<NF, TAPS>(sm->pre + OFF0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
                                  otile + fl * p.nceptrums, p.nceptrums, p.taps, g.f0 + fl);
         __syncthreads();
     }
@@ -268,13 +288,13 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
 // computed.
 struct SmemF {
     mfccf::DevTablesF tab;
-    alignas(16) int16_t raw[2][RAWN];
-    alignas(16) float xbuf[WARPS][mfccf::XWF];
+    alignas(16) int16_t raw[2][RAWN_F];
+    alignas(16) float xbuf[WARPS_F][mfccf::XWF];
     alignas(8) uint64_t mbar[2];
 };
 
 __device__ __forceinline__ void issue_tile_f(const RunParams &p, const TileIter &it, SmemF *sm, int buf) {
-    const Tile g = tile_geo(p, it.ci, it.ti);
+    const Tile g = tile_geo<FT_F>(p, it.ci, it.ti);
     const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
     if (bytes) {
         mbar_arrive_expect_tx(&sm->mbar[buf], bytes);
@@ -285,7 +305,7 @@ __device__ __forceinline__ void issue_tile_f(const RunParams &p, const TileIter 
 }
 
 template <int NF>
-__global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
+__global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const RunParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     SmemF *sm = reinterpret_cast<SmemF *>(smem_raw);
@@ -293,11 +313,11 @@ __global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
     {
         const int4 *src = reinterpret_cast<const int4 *>(p.ftab);
         int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
-        for (int i = tid; i < (int)(sizeof(mfccf::DevTablesF) / 16); i += THREADS) dst[i] = src[i];
+        for (int i = tid; i < (int)(sizeof(mfccf::DevTablesF) / 16); i += THREADS_F) dst[i] = src[i];
     }
     // The padded power area has gaps no frame ever writes; the mel walk reads them with
     // zero weights, so they must hold finite numbers (0 * NaN would poison the sum).
-    for (int i = tid; i < WARPS * mfccf::PW_WORDS; i += THREADS)
+    for (int i = tid; i < WARPS_F * mfccf::PW_WORDS; i += THREADS_F)
         sm->xbuf[i / mfccf::PW_WORDS][mfccf::PW_OFF + i % mfccf::PW_WORDS] = 0.0f;
     if (tid == 0) { mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1); }
     __syncthreads();
@@ -307,11 +327,11 @@ __global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
     if (tid == 0 && ti.tile < p.n_tiles) issue_tile_f(p, ti, sm, 0);
     for (int it = 0; ti.tile < p.n_tiles; ++it) {
         const int buf = it & 1;
-        const Tile g = tile_geo(p, ti.ci, ti.ti);
+        const Tile g = tile_geo<FT_F>(p, ti.ci, ti.ti);
         ti.next();
         int16_t *raw = sm->raw[buf];
-        for (int j = tid; j < g.lo; j += THREADS) raw[j] = 0;
-        for (int j = g.hi + tid; j < g.len; j += THREADS) {
+        for (int j = tid; j < g.lo; j += THREADS_F) raw[j] = 0;
+        for (int j = g.hi + tid; j < g.len; j += THREADS_F) {
             const long long s = g.a0 + j;
             raw[j] = (s >= 0 && s < p.n_samples) ? g.clip[s] : (int16_t)0;
         }
@@ -319,10 +339,9 @@ __global__ void __launch_bounds__(THREADS, 3) mfcc_f32_fused(const RunParams p)
         if (tid == 0 && ti.tile < p.n_tiles) issue_tile_f(p, ti, sm, buf ^ 1);
         mbar_wait(&sm->mbar[buf], (uint32_t)(it >> 1) & 1u);
         __syncthreads();
-        const int off0 = (int)(HOP * g.f0 - g.a0);          // even, 8..14
         float *otile = static_cast<float *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
-        for (int fl = warp; fl < g.nf; fl += WARPS) {
-            mfccf::power_warp_f32(raw + off0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane);
+        for (int fl = warp; fl < g.nf; fl += WARPS_F) {
+            mfccf::power_warp_f32(raw + OFF0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane);
             const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, sm->xbuf[warp], &sm->tab, lane);
             if (lane < p.nceptrums) otile[fl * p.nceptrums + lane] = c;
             __syncwarp();
@@ -868,8 +887,7 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
     if (n_clips > 1 && (clip_stride < n_samples || out_clip_stride < n_frames * h->cfg.nceptrums))
         return fail(MFCC_B200_EINVAL, "row pitch smaller than the row");
     if (taps && n_clips != 1) return fail(MFCC_B200_EINVAL, "taps need n_clips == 1");
-    const bool f32 = h->cfg.mode == MFCC_B200_MODE_FP32;
-    if (taps && f32) return fail(MFCC_B200_EUNSUPPORTED, "taps are an integer-mode feature");
+    if (taps && h->cfg.mode == MFCC_B200_MODE_FP32) return fail(MFCC_B200_EUNSUPPORTED, "taps are an integer-mode feature");
     if (HOP * (n_frames - 1) + NFFT > (1LL << 40)) return fail(MFCC_B200_EINVAL, "clip too long");
 
     RunParams p;
@@ -877,16 +895,18 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
     p.x = d_x; p.clip_stride = clip_stride; p.n_samples = n_samples; p.n_frames = n_frames;
     p.out = d_out; p.out_clip_stride = out_clip_stride;
     p.tab = h->d_tab; p.ftab = h->d_ftab; p.nceptrums = h->cfg.nceptrums;
-    p.tiles_per_clip = (int)((n_frames + FT - 1) / FT);
+    const bool f32 = h->cfg.mode == MFCC_B200_MODE_FP32;
+    const int ft = f32 ? FT_F : FT;
+    p.tiles_per_clip = (int)((n_frames + ft - 1) / ft);
     p.n_tiles = (long long)p.tiles_per_clip * n_clips;
     p.aligned = ((reinterpret_cast<uintptr_t>(d_x) & 15) == 0) && (n_clips == 1 || (clip_stride % 8) == 0);
     if (taps) p.taps = *taps;
-    long long grid = (long long)h->sm_count * (f32 ? 3 : CTAS_PER_SM);
+    long long grid = (long long)h->sm_count * (f32 ? CTAS_PER_SM_F : CTAS_PER_SM);
     if (grid > p.n_tiles) grid = p.n_tiles;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (f32) {
-        if (h->cfg.nfilters == 32) mfcc_f32_fused<32><<<(unsigned)grid, THREADS, sizeof(SmemF), s>>>(p);
-        else                       mfcc_f32_fused<16><<<(unsigned)grid, THREADS, sizeof(SmemF), s>>>(p);
+        if (h->cfg.nfilters == 32) mfcc_f32_fused<32><<<(unsigned)grid, THREADS_F, sizeof(SmemF), s>>>(p);
+        else                       mfcc_f32_fused<16><<<(unsigned)grid, THREADS_F, sizeof(SmemF), s>>>(p);
     } else {
         const bool nf32 = h->cfg.nfilters == 32;
         if (taps && nf32)  mfcc_int_fused<32, true><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
