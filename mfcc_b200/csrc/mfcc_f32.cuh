@@ -91,40 +91,57 @@ __device__ __forceinline__ float2 emph_win(unsigned w, unsigned wprev, float w0,
 __device__ __forceinline__ int zaddr(int k) { return k + ((k >> 6) << 2); }
 
 // ---------------------------------------------------------------------------------
-// Power spectrum |X[b]|^2 / 512^2, b = 0..256, of one frame into pw[] (shared memory).
-//   raw: the frame's int16 samples in shared memory (even halfword offset), raw[-1] is
-//        the sample before the frame (0 at the start of a stream)
-__device__ __forceinline__ void power_warp_f32(const int16_t *raw, float *xb, const DevTablesF *tab, int lane)
+// Power spectrum |X[b]|^2 / 512^2, b = 0..256, of NFR frames into pw[] (shared memory).
+//   raw[f]: frame f's int16 samples in shared memory (even halfword offset), raw[f][-1] is
+//           the sample before the frame (0 at the start of a stream)
+//   xb[f]:  frame f's exchange buffer (XWF words)
+// The kernel is bound by shared-memory bandwidth, and more than half of a frame's
+// wavefronts are loads of tables that do not depend on the frame (window, twiddles, mel
+// weights, DCT matrix, layout addresses).  With NFR = 2 a warp carries two frames through
+// every phase together and loads each table entry once for both.
+template <int NFR>
+__device__ __forceinline__ void power_warp_f32(const int16_t *const (&raw)[NFR], float *const (&xb)[NFR],
+                                               const DevTablesF *tab, int lane)
 {
-    float2 *xc = reinterpret_cast<float2 *>(xb);
-    float *pw = xb + PW_OFF;
-    const unsigned *r32 = reinterpret_cast<const unsigned *>(raw);
     const float2 *win2 = reinterpret_cast<const float2 *>(tab->window);
     // ---- z[n] = (y[2n] w[2n], y[2n+1] w[2n+1]), n = lane + 32 a
-    float2 v[8];
+    float2 v[NFR][8];
 #pragma unroll
     for (int a = 0; a < 8; ++a) {
         const int n = lane + 32 * a;
         const float2 ww = win2[n];
-        v[a] = emph_win(r32[n], r32[n - 1], ww.x, ww.y);
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            const unsigned *r32 = reinterpret_cast<const unsigned *>(raw[f]);
+            v[f][a] = emph_win(r32[n], r32[n - 1], ww.x, ww.y);
+        }
     }
     // ---- pass 1: DFT-8 over a, twiddle W256^(lane * k1), transpose
-    fft8(v);
+#pragma unroll
+    for (int f = 0; f < NFR; ++f) fft8(v[f]);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int k1 = brev3(j);
-        float2 y = v[j];
-        if (k1) y = cmul(y, tab->twA[k1 * 32 + lane]);
-        xc[k1 * T1_STRIDE + lane] = y;
+        float2 w = make_float2(1.0f, 0.0f);
+        if (k1) w = tab->twA[k1 * 32 + lane];
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            float2 y = v[f][j];
+            if (k1) y = cmul(y, w);
+            reinterpret_cast<float2 *>(xb[f])[k1 * T1_STRIDE + lane] = y;
+        }
     }
     __syncwarp();
     // lane = (k1, c): the 8 values l = c + 4 b of row k1
     const int k1 = lane >> 2, c = lane & 3;
 #pragma unroll
-    for (int b = 0; b < 8; ++b) v[b] = xc[k1 * T1_STRIDE + c + 4 * b];
+    for (int f = 0; f < NFR; ++f)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) v[f][b] = reinterpret_cast<const float2 *>(xb[f])[k1 * T1_STRIDE + c + 4 * b];
     __syncwarp();
     // ---- pass 2: DFT-8 over b, twiddle W32^(c p) = W256^(8 c p)
-    fft8(v);
+#pragma unroll
+    for (int f = 0; f < NFR; ++f) fft8(v[f]);
     // ---- pass 3: DFT-4 over c across the four lanes of a group; lane c ends with
     //      q = {0, 2, 1, 3}[c] of Z[k1 + 8 p + 64 q]
     const float sg = (c & 2) ? -1.0f : 1.0f, sg1 = (c & 1) ? -1.0f : 1.0f;
@@ -132,17 +149,22 @@ __device__ __forceinline__ void power_warp_f32(const int16_t *raw, float *xb, co
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int p = brev3(j);
-        float2 y = v[j];
-        if (p) y = cmul(y, tab->twB[p * 4 + c]);
-        float2 o;
-        o.x = __shfl_xor_sync(FULL, y.x, 2);
-        o.y = __shfl_xor_sync(FULL, y.y, 2);
-        y = make_float2(fmaf(sg, y.x, o.x), fmaf(sg, y.y, o.y));     // c<2: mine+other, else other-mine
-        if (c == 3) y = mul_mj(y);
-        o.x = __shfl_xor_sync(FULL, y.x, 1);
-        o.y = __shfl_xor_sync(FULL, y.y, 1);
-        y = make_float2(fmaf(sg1, y.x, o.x), fmaf(sg1, y.y, o.y));
-        xc[zaddr(k1 + 8 * p + 64 * q)] = y;
+        float2 w = make_float2(1.0f, 0.0f);
+        if (p) w = tab->twB[p * 4 + c];
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            float2 y = v[f][j];
+            if (p) y = cmul(y, w);
+            float2 o;
+            o.x = __shfl_xor_sync(FULL, y.x, 2);
+            o.y = __shfl_xor_sync(FULL, y.y, 2);
+            y = make_float2(fmaf(sg, y.x, o.x), fmaf(sg, y.y, o.y));     // c<2: mine+other, else other-mine
+            if (c == 3) y = mul_mj(y);
+            o.x = __shfl_xor_sync(FULL, y.x, 1);
+            o.y = __shfl_xor_sync(FULL, y.y, 1);
+            y = make_float2(fmaf(sg1, y.x, o.x), fmaf(sg1, y.y, o.y));
+            reinterpret_cast<float2 *>(xb[f])[zaddr(k1 + 8 * p + 64 * q)] = y;
+        }
     }
     __syncwarp();
     // ---- split: X[k] = F + W512^k G, X[256-k] = conj(F - W512^k G), with
@@ -151,90 +173,127 @@ __device__ __forceinline__ void power_warp_f32(const int16_t *raw, float *xb, co
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int k = lane + 32 * i;
-        const float2 A = xc[zaddr(k)];
-        const float2 B = xc[zaddr((256 - k) & 255)];
         const float2 w = tab->tw512[k];
-        const float2 F = make_float2(0.5f * (A.x + B.x), 0.5f * (A.y - B.y));
-        const float2 G = make_float2(0.5f * (A.y + B.y), -0.5f * (A.x - B.x));
-        const float2 T = cmul(G, w);
-        const float2 X0 = cadd(F, T), X1 = csub(F, T);
-        pw[tab->paddr[k]] = (X0.x * X0.x + X0.y * X0.y) * SC;
-        pw[tab->paddr[256 - k]] = (X1.x * X1.x + X1.y * X1.y) * SC;      // k = 0 gives bin 256
+        const int pa = tab->paddr[k], pb = tab->paddr[256 - k];          // k = 0 gives bin 256
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            const float2 *xc = reinterpret_cast<const float2 *>(xb[f]);
+            float *pw = xb[f] + PW_OFF;
+            const float2 A = xc[zaddr(k)];
+            const float2 B = xc[zaddr((256 - k) & 255)];
+            const float2 F = make_float2(0.5f * (A.x + B.x), 0.5f * (A.y - B.y));
+            const float2 G = make_float2(0.5f * (A.y + B.y), -0.5f * (A.x - B.x));
+            const float2 T = cmul(G, w);
+            const float2 X0 = cadd(F, T), X1 = csub(F, T);
+            pw[pa] = (X0.x * X0.x + X0.y * X0.y) * SC;
+            pw[pb] = (X1.x * X1.x + X1.y * X1.y) * SC;
+        }
     }
     if (lane == 0) {                                         // bin 128: W512^128 = -j
-        const float2 A = xc[zaddr(128)];
-        pw[tab->paddr[128]] = (A.x * A.x + A.y * A.y) * SC;
+        const int pa = tab->paddr[128];
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            const float2 A = reinterpret_cast<const float2 *>(xb[f])[zaddr(128)];
+            xb[f][PW_OFF + pa] = (A.x * A.x + A.y * A.y) * SC;
+        }
     }
     __syncwarp();
 }
 
-// mel -> log2 -> DCT-II of the power spectrum in pw[] (padded layout); lane k returns
-// coefficient k.  The filters are triangles (cell 7): bin b of segment g (the bins
+// mel -> log2 -> DCT-II of the power spectra in xb[f] + PW_OFF (padded layout); lane k gets
+// coefficient k of frame f in out[f]; xb[f][0..NF) is scratch.  The filters are triangles
+// (cell 7): bin b of segment g (the bins
 // between two filter points) carries the rising weight of filter g and the falling
 // weight of filter g-1, so lane g-1 walks segment g once with two multiply-adds per
 // bin (weights zero-padded to MAXSEG steps: no branches) and filter m is the rising sum
 // of segment m, taken from the neighbouring lane, plus the falling sum of segment m+1.
 // The padded layout (DevTablesF::paddr) starts every segment in a bank of its own, so the
 // 32 lanes read 32 different banks at every step.
-template <int NF>
-__device__ __forceinline__ float cepstrum_warp_f32(float *pw, float *lbuf, const DevTablesF *tab, int lane)
+template <int NF, int NFR>
+__device__ __forceinline__ void cepstrum_warp_f32(float *const (&xb)[NFR], const DevTablesF *tab, int lane,
+                                                  float (&out)[NFR])
 {
     constexpr int MAXSEG = (NF == 32) ? 21 : 42;
     const int li = lane & (NF - 1);
-    const float *p = pw + tab->seg_base[li];
-    float u = 0.0f, v = 0.0f;
+    const int sb = tab->seg_base[li];
+    float u[NFR], v[NFR];
+#pragma unroll
+    for (int f = 0; f < NFR; ++f) u[f] = v[f] = 0.0f;
     if (NF == 32) {
 #pragma unroll
         for (int j = 0; j < MEL_J0; ++j) {
-            const float d = p[j];
             const float2 w = tab->melw[j * NF + li];
-            u = fmaf(d, w.x, u);
-            v = fmaf(d, w.y, v);
+#pragma unroll
+            for (int f = 0; f < NFR; ++f) {
+                const float d = xb[f][PW_OFF + sb + j];
+                u[f] = fmaf(d, w.x, u[f]);
+                v[f] = fmaf(d, w.y, v[f]);
+            }
         }
         // only the long segments of the upper filters go on: with the lower half-warp
         // predicated off a 64-bit weight load is one shared-memory wavefront, not two
         if (lane >= tab->mel_tail_lane) {
 #pragma unroll
             for (int j = MEL_J0; j < MAXSEG; ++j) {
-                const float d = p[j];
                 const float2 w = tab->melw[j * NF + li];
-                u = fmaf(d, w.x, u);
-                v = fmaf(d, w.y, v);
+#pragma unroll
+                for (int f = 0; f < NFR; ++f) {
+                    const float d = xb[f][PW_OFF + sb + j];
+                    u[f] = fmaf(d, w.x, u[f]);
+                    v[f] = fmaf(d, w.y, v[f]);
+                }
             }
         }
     } else {
         const int j0 = (lane >> 4) * (MAXSEG / 2);
 #pragma unroll
         for (int j = 0; j < MAXSEG / 2; ++j) {
-            const float d = p[j0 + j];
             const float2 w = tab->melw[(j0 + j) * NF + li];
-            u = fmaf(d, w.x, u);
-            v = fmaf(d, w.y, v);
+#pragma unroll
+            for (int f = 0; f < NFR; ++f) {
+                const float d = xb[f][PW_OFF + sb + j0 + j];
+                u[f] = fmaf(d, w.x, u[f]);
+                v[f] = fmaf(d, w.y, v[f]);
+            }
         }
-        u += __shfl_xor_sync(FULL, u, 16);
-        v += __shfl_xor_sync(FULL, v, 16);
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            u[f] += __shfl_xor_sync(FULL, u[f], 16);
+            v[f] += __shfl_xor_sync(FULL, v[f], 16);
+        }
     }
     // lane 0 walks segment 0 as well (its rise weights sit in the fall slot: both feed
     // filter 0), so it takes nothing from a neighbour
-    float up = __shfl_up_sync(FULL, u, 1);
-    if (li == 0) up = 0.0f;
-    const float L = __log2f(fmaxf(up + v, tab->mel_floor));
+#pragma unroll
+    for (int f = 0; f < NFR; ++f) {
+        float up = __shfl_up_sync(FULL, u[f], 1);
+        if (li == 0) up = 0.0f;
+        xb[f][lane] = __log2f(fmaxf(up + v[f], tab->mel_floor));
+    }
     // orthonormal DCT-II with D[k][NF-1-n] = (-1)^k D[k][n]: NF/2 multiply-adds per lane
-    lbuf[lane] = L;
     __syncwarp();
     const float sg = (li & 1) ? -1.0f : 1.0f;
-    float out = 0.0f;
+#pragma unroll
+    for (int f = 0; f < NFR; ++f) out[f] = 0.0f;
 #pragma unroll
     for (int q = 0; q < NF / 8; ++q) {
-        const float4 a = reinterpret_cast<const float4 *>(lbuf)[q];                       // L[4q .. 4q+3]
-        const float4 b = reinterpret_cast<const float4 *>(lbuf)[NF / 4 - 1 - q];          // L[NF-4-4q .. NF-1-4q]
-        out = fmaf(fmaf(sg, b.w, a.x), tab->dct[(4 * q + 0) * 32 + li], out);
-        out = fmaf(fmaf(sg, b.z, a.y), tab->dct[(4 * q + 1) * 32 + li], out);
-        out = fmaf(fmaf(sg, b.y, a.z), tab->dct[(4 * q + 2) * 32 + li], out);
-        out = fmaf(fmaf(sg, b.x, a.w), tab->dct[(4 * q + 3) * 32 + li], out);
+        float4 a[NFR], b[NFR];
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            a[f] = reinterpret_cast<const float4 *>(xb[f])[q];                       // L[4q .. 4q+3]
+            b[f] = reinterpret_cast<const float4 *>(xb[f])[NF / 4 - 1 - q];          // L[NF-4-4q .. NF-1-4q]
+        }
+        const float d0 = tab->dct[(4 * q + 0) * 32 + li], d1 = tab->dct[(4 * q + 1) * 32 + li];
+        const float d2 = tab->dct[(4 * q + 2) * 32 + li], d3 = tab->dct[(4 * q + 3) * 32 + li];
+#pragma unroll
+        for (int f = 0; f < NFR; ++f) {
+            out[f] = fmaf(fmaf(sg, b[f].w, a[f].x), d0, out[f]);
+            out[f] = fmaf(fmaf(sg, b[f].z, a[f].y), d1, out[f]);
+            out[f] = fmaf(fmaf(sg, b[f].y, a[f].z), d2, out[f]);
+            out[f] = fmaf(fmaf(sg, b[f].x, a[f].w), d3, out[f]);
+        }
     }
     __syncwarp();
-    return out;
 }
 
 }  // namespace mfccf

@@ -34,15 +34,19 @@ constexpr int CTAS_PER_SM = 4;
 #define MFCC_F32_WARPS 8
 #endif
 #ifndef MFCC_F32_FT
-#define MFCC_F32_FT 24
+#define MFCC_F32_FT 32
+#endif
+#ifndef MFCC_F32_NFR
+#define MFCC_F32_NFR 2               // frames a warp carries through the chain together
 #endif
 constexpr int WARPS_F   = MFCC_F32_WARPS;
 constexpr int THREADS_F = WARPS_F * 32;
 constexpr int FT_F      = MFCC_F32_FT;
 constexpr int RAWN_F    = ((HOP * (FT_F - 1) + NFFT + 15) + 7) & ~7;
 #ifndef MFCC_F32_CTAS
-#define MFCC_F32_CTAS 3
+#define MFCC_F32_CTAS 2
 #endif
+constexpr int NFR_F = MFCC_F32_NFR;
 constexpr int CTAS_PER_SM_F = MFCC_F32_CTAS;
 
 struct RunParams {
@@ -106,6 +110,7 @@ struct Tile {
 // A tile starts FT * HOP samples after the previous one, a multiple of 8: raw[0] is always the
 // sample 8 before the tile's first frame, so every bulk copy is 16-byte aligned on both sides.
 static_assert((FT * HOP) % 8 == 0 && (FT_F * HOP) % 8 == 0, "tiles must start on 16-byte boundaries of the clip");
+static_assert(FT_F % (NFR_F * WARPS_F) == 0, "every frame a warp touches must lie inside the tile buffer");
 constexpr int OFF0 = 8;                                      // raw[OFF0] = first sample of the tile's first frame
 template <int FTT = FT>
 __device__ __forceinline__ Tile tile_geo(const RunParams &p, long long ci, int ti) {
@@ -289,7 +294,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
 struct SmemF {
     mfccf::DevTablesF tab;
     alignas(16) int16_t raw[2][RAWN_F];
-    alignas(16) float xbuf[WARPS_F][mfccf::XWF];
+    alignas(16) float xbuf[WARPS_F][NFR_F][mfccf::XWF];
     alignas(8) uint64_t mbar[2];
 };
 
@@ -317,8 +322,8 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
     }
     // The padded power area has gaps no frame ever writes; the mel walk reads them with
     // zero weights, so they must hold finite numbers (0 * NaN would poison the sum).
-    for (int i = tid; i < WARPS_F * mfccf::PW_WORDS; i += THREADS_F)
-        sm->xbuf[i / mfccf::PW_WORDS][mfccf::PW_OFF + i % mfccf::PW_WORDS] = 0.0f;
+    for (int i = tid; i < WARPS_F * NFR_F * mfccf::PW_WORDS; i += THREADS_F)
+        (&sm->xbuf[0][0][0])[(i / mfccf::PW_WORDS) * mfccf::XWF + mfccf::PW_OFF + i % mfccf::PW_WORDS] = 0.0f;
     if (tid == 0) { mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1); }
     __syncthreads();
 
@@ -340,11 +345,22 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
         mbar_wait(&sm->mbar[buf], (uint32_t)(it >> 1) & 1u);
         __syncthreads();
         float *otile = static_cast<float *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
-        for (int fl = warp; fl < g.nf; fl += WARPS_F) {
-            mfccf::power_warp_f32(raw + OFF0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane);
-            const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, sm->xbuf[warp], &sm->tab, lane);
-            if (lane < p.nceptrums) otile[fl * p.nceptrums + lane] = c;
-            __syncwarp();
+        // a warp takes frames fl, fl + WARPS_F, ... NFR_F at a time; a frame past the end of the
+        // tile is computed on whatever the buffer holds and not stored
+        for (int fl = warp; fl < g.nf; fl += NFR_F * WARPS_F) {
+            const int16_t *fr[NFR_F];
+            float *xb[NFR_F];
+#pragma unroll
+            for (int f = 0; f < NFR_F; ++f) {
+                fr[f] = raw + OFF0 + HOP * (fl + f * WARPS_F);
+                xb[f] = sm->xbuf[warp][f];
+            }
+            float c[NFR_F];
+            mfccf::power_warp_f32<NFR_F>(fr, xb, &sm->tab, lane);
+            mfccf::cepstrum_warp_f32<NF, NFR_F>(xb, &sm->tab, lane, c);
+#pragma unroll
+            for (int f = 0; f < NFR_F; ++f)
+                if (lane < p.nceptrums && fl + f * WARPS_F < g.nf) otile[(fl + f * WARPS_F) * p.nceptrums + lane] = c[f];
         }
         __syncthreads();
     }
@@ -531,10 +547,12 @@ __global__ void __launch_bounds__(THREADS) mfcc_f32_step(int16_t *state, const i
         __syncwarp();
         // new state = raw(HOP-1 .. 511)
         for (int i = lane; i <= HIST; i += 32) st[i] = raw[2 + i + HOP - 1];
-        mfccf::power_warp_f32(raw + 2, sm->xbuf[warp], &sm->tab, lane);
-        const float c = mfccf::cepstrum_warp_f32<NF>(sm->xbuf[warp] + mfccf::PW_OFF, sm->xbuf[warp], &sm->tab, lane);
-        if (lane < nceptrums) out[(long long)s * nceptrums + lane] = c;
-        __syncwarp();
+        const int16_t *fr[1] = {raw + 2};
+        float *xb[1] = {sm->xbuf[warp]};
+        float c[1];
+        mfccf::power_warp_f32<1>(fr, xb, &sm->tab, lane);
+        mfccf::cepstrum_warp_f32<NF, 1>(xb, &sm->tab, lane, c);
+        if (lane < nceptrums) out[(long long)s * nceptrums + lane] = c[0];
     }
 }
 
