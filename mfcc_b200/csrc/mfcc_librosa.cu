@@ -381,6 +381,72 @@ lr_dct(const float *__restrict__ logmel, const int *__restrict__ clipmax, int n_
     }
 }
 
+// The same product for the default shape (128 mel bands, 32 coefficients) with the DCT matrix
+// in the kernel's parameter space (16 KB of constant bank 0): lane = frame, 32 accumulators per
+// lane, the weights are constant-bank operands of the multiply-adds, so the inner loop has one
+// shared-memory load per 32 multiply-adds.  A warp takes 32 consecutive frames: their clamped
+// rows are transposed through shared memory ([band][frame], pitch 33).  Summation order per
+// coefficient is the same as lr_dct's (ascending band), so the results are identical.
+constexpr int DC_MELS = 128, DC_MFCC = 32, DC_WARPS = 4, DC_PITCH = 33;
+struct alignas(16) LrDctParam { float4 D[DC_MELS * DC_MFCC / 4]; };   // [band][coefficient], four coefficients per entry
+__global__ void __launch_bounds__(DC_WARPS * 32)
+lr_dct_c(const float *__restrict__ logmel, const int *__restrict__ clipmax, long long total, long long n_frames,
+         float top_db, const __grid_constant__ LrDctParam prm, float *__restrict__ out, long long out_clip_stride)
+{
+    extern __shared__ __align__(16) float dsm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *xT = dsm + warp * (DC_MELS * DC_PITCH);
+    const long long groups = (total + 31) / 32;
+    for (long long g = (long long)blockIdx.x * DC_WARPS + warp; g < groups; g += (long long)gridDim.x * DC_WARPS) {
+        const long long item0 = g * 32;
+        // lane j's frame: clip and frame index, and the dB floor of its clip
+        const long long my_item = item0 + lane;
+        const long long my_clip = (my_item < total ? my_item : total - 1) / n_frames;
+        const long long my_f = my_item - my_clip * n_frames;
+        const float my_floor = top_db >= 0.0f ? key_float(clipmax[my_clip]) - top_db : -3.0e38f;
+        // eight rows at a time: 32 independent global loads in flight per lane
+#pragma unroll 1
+        for (int jb = 0; jb < 32; jb += 8) {
+            float r[8][DC_MELS / 32];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const long long item = item0 + jb + j < total ? item0 + jb + j : total - 1;
+                const float *row = logmel + item * DC_MELS;
+#pragma unroll
+                for (int c = 0; c < DC_MELS / 32; ++c) r[j][c] = row[lane + 32 * c];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float floor_db = __shfl_sync(0xffffffffu, my_floor, jb + j);
+#pragma unroll
+                for (int c = 0; c < DC_MELS / 32; ++c) xT[(lane + 32 * c) * DC_PITCH + jb + j] = fmaxf(r[j][c], floor_db);
+            }
+        }
+        __syncwarp();
+        float acc[DC_MFCC];
+#pragma unroll
+        for (int k = 0; k < DC_MFCC; ++k) acc[k] = 0.0f;
+#pragma unroll 4
+        for (int n = 0; n < DC_MELS; ++n) {
+            const float x = xT[n * DC_PITCH + lane];
+#pragma unroll
+            for (int k = 0; k < DC_MFCC; k += 4) {
+                const float4 d = prm.D[n * (DC_MFCC / 4) + (k >> 2)];       // uniform 128-bit constant load
+                acc[k] = fmaf(d.x, x, acc[k]);
+                acc[k + 1] = fmaf(d.y, x, acc[k + 1]);
+                acc[k + 2] = fmaf(d.z, x, acc[k + 2]);
+                acc[k + 3] = fmaf(d.w, x, acc[k + 3]);
+            }
+        }
+        if (item0 + lane < total) {
+            float4 *o = reinterpret_cast<float4 *>(out + my_clip * out_clip_stride + my_f * DC_MFCC);
+#pragma unroll
+            for (int k = 0; k < DC_MFCC; k += 4) o[k >> 2] = make_float4(acc[k], acc[k + 1], acc[k + 2], acc[k + 3]);
+        }
+        __syncwarp();
+    }
+}
+
 __global__ void lr_init_max(int *clipmax, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) clipmax[i] = (int)0x80000000;
@@ -396,6 +462,8 @@ struct LrHandle {
     float amin, top_db;
     LrDev dev;
     std::vector<void *> allocs;
+    LrDctParam *dct_param = nullptr;            // host copy of the DCT matrix for lr_dct_c (default shape only)
+    ~LrHandle() { delete dct_param; }
 };
 
 }  // namespace
@@ -554,6 +622,13 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas1, h->logmel, LR_THREADS, h->smem1);
     if (e == cudaSuccess && h->ctas1 < 1) h->ctas1 = 1;
     h->dev.dct = (float *)upload(dT.data(), dT.size() * sizeof(float));
+    if (h->n_mels == DC_MELS && h->n_mfcc == DC_MFCC) {
+        h->dct_param = new LrDctParam;
+        memcpy(h->dct_param->D, dT.data(), sizeof(LrDctParam));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lr_dct_c, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(DC_WARPS * DC_MELS * DC_PITCH * sizeof(float)));
+    }
     if (e != cudaSuccess) {
         for (void *p : h->allocs) cudaFree(p);
         delete h;
@@ -617,11 +692,20 @@ int mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_stride,
                                                   h->n_mels, h->amin, h->dev, logmel, clipmax,
                                                   taps ? taps->d_power : nullptr);
     mfccb_host::count_launch();
-    long long g2 = (total + 31) / 32;
-    if (g2 > (long long)h->sms * 8) g2 = (long long)h->sms * 8;
-    const size_t dsm = ((((size_t)h->n_mels * h->n_mfcc + 3) & ~(size_t)3) + 8 * 4 * (size_t)h->n_mels) * sizeof(float);
-    lr_dct<<<(unsigned)g2, 256, dsm, st>>>(logmel, clipmax, n_clips, n_frames, h->n_mels, h->n_mfcc, h->top_db, h->dev,
-                                           d_out, out_clip_stride);
+    // float4 stores of whole rows: the output rows must be 16-byte aligned for lr_dct_c
+    const bool rows16 = (reinterpret_cast<uintptr_t>(d_out) & 15) == 0 && (out_clip_stride % 4) == 0;
+    if (h->dct_param && rows16) {
+        long long g2 = (total + 32 * DC_WARPS - 1) / (32 * DC_WARPS);
+        if (g2 > (long long)h->sms * 3) g2 = (long long)h->sms * 3;
+        lr_dct_c<<<(unsigned)g2, DC_WARPS * 32, DC_WARPS * DC_MELS * DC_PITCH * sizeof(float), st>>>(
+            logmel, clipmax, total, n_frames, h->top_db, *h->dct_param, d_out, out_clip_stride);
+    } else {
+        long long g2 = (total + 31) / 32;
+        if (g2 > (long long)h->sms * 8) g2 = (long long)h->sms * 8;
+        const size_t dsm = ((((size_t)h->n_mels * h->n_mfcc + 3) & ~(size_t)3) + 8 * 4 * (size_t)h->n_mels) * sizeof(float);
+        lr_dct<<<(unsigned)g2, 256, dsm, st>>>(logmel, clipmax, n_clips, n_frames, h->n_mels, h->n_mfcc, h->top_db, h->dev,
+                                               d_out, out_clip_stride);
+    }
     mfccb_host::count_launch();
     if (taps && taps->d_logmel)
         cudaMemcpyAsync(taps->d_logmel, logmel, (size_t)total * h->n_mels * sizeof(float), cudaMemcpyDeviceToDevice, st);
