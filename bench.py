@@ -377,7 +377,7 @@ def main():
             tl = timed(lambda: opl(xl, out=outl))
             return {"value": nl * Kl / tl, "unit": "frames/s", "ms_per_step": tl * 1e3,
                     "clips": nl, "frames_per_clip": Kl, "steps": fsteps,
-                    "kernels": ["lr_logmel", "lr_dct"], "finite": bool(torch.isfinite(outl[:64]).all())}
+                    "kernels": ["lr_logmel", "lr_dct_c"], "finite": bool(torch.isfinite(outl[:64]).all())}
 
         def leg_stream_fp32():
             opf = mfcc_b200.MFCC(nfilters=NFILT, nceptrums=NCEP, mode="fp32", mel_floor=1e-3, device=dev)

@@ -7,6 +7,7 @@ python -m pytest tests -m gpu -q 2>&1 | tail -3 | tee $o/${tag}_pytest.txt
 python bench.py --impl reference > $o/${tag}_bench_reference.json 2> $o/${tag}_bench_reference.err
 python bench.py > $o/${tag}_bench_full.json 2> $o/${tag}_bench_full.err || tail -5 $o/${tag}_bench_full.err
 tail -c 600 $o/${tag}_bench_full.json
+[ -x profiles/micro/pipe_bench ] || nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o profiles/micro/pipe_bench profiles/micro/pipe_bench.cu
 profiles/micro/pipe_bench > $o/${tag}_pipe_bench.jsonl
 # launch list of the bench command, this library's kernels only (the synthetic-data generation is
 # thousands of torch launches); cold-cache, serialised: shares, not absolutes

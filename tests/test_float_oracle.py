@@ -97,6 +97,26 @@ def test_cuda_fp32_other_filter_sets(wav, nf, nc):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("K", [1, 7, 8, 9, 15, 16, 17, 31, 32, 33, 47, 48, 49, 65])
+def test_cuda_fp32_frame_counts_around_the_tile_and_the_frame_pairs(wav, K):
+    """The fp32 kernel cuts a clip into 32-frame tiles and a warp carries frames f and f + 8
+    together; every frame count around those sizes, two clips per launch, each frame equal to the
+    same frame of a one-clip launch (the tiling is invisible) and inside the tolerance."""
+    import torch
+    import mfcc_b200
+    n = 512 + 170 * (K - 1) + 3
+    x = np.stack([wav[40000:40000 + n], wav[90000:90000 + n]])
+    op = mfcc_b200.MFCC(nfilters=32, nceptrums=32, mode="fp32", mel_floor=1e-3, device="cuda:0")
+    got = op(torch.from_numpy(np.ascontiguousarray(x)).to("cuda:0")).cpu().numpy()
+    assert got.shape == (2, K, 32)
+    for i in range(2):
+        one = op(torch.from_numpy(np.ascontiguousarray(x[i])).to("cuda:0")).cpu().numpy()
+        assert np.array_equal(one, got[i])
+        ref, t = F.mfcc(x[i], mel_floor=1e-3, taps=True)
+        _check(got[i].astype(np.float64), ref, t["mel"])
+
+
+@pytest.mark.gpu
 def test_cuda_fp32_batch_ragged_floor_and_host(wav):
     import torch
     import mfcc_b200

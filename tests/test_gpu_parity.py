@@ -75,10 +75,11 @@ def test_edge_clips_batched(ops, RC, key):
         assert np.array_equal(got[i], want[i]), name
 
 
-@pytest.mark.parametrize("n", [0, 1, 511, 512, 513, 681, 682, 683, 1000, 5951, 5952, 5953, 6121,
-                               6122, 11393, 20001])
+@pytest.mark.parametrize("n", [0, 1, 511, 512, 513, 681, 682, 683, 1000, 4421, 4422, 4423, 4591, 4592, 4593,
+                               5951, 5952, 5953, 6121, 6122, 8671, 8672, 8673, 11393, 20001])
 def test_ragged_lengths_and_tile_boundaries(ops, RC, n):
-    """n around nfft, the hop and the 32-frame tile boundary (5952 = 170*32+512)."""
+    """n around nfft, the hop and the tile boundaries: a tile is 24 frames (4422 = 170*23+512 fills
+    one, 4592 starts the second, 8672 the third); 5952 = 170*32+512 is the fp32 kernel's tile."""
     m = ops[(32, 32)]
     cfg = RC.RefConfig()
     rng = np.random.default_rng(n)
