@@ -26,10 +26,10 @@ struct alignas(16) DevTables {
     int2     tw8[256];       // stage 8, doubled, natural order
     uint2    melab[704];     // FilterBank weights, padded per segment: see mel_warp()
     uint32_t pad0[4];
-    uint16_t logfrac[2048];  // Log2Fix fraction bits 10..1 for every 12-bit mantissa: see log2fix_tab()
+    alignas(16) uint16_t logfrac[2048];  // Log2Fix fraction bits 10..1 for every 12-bit mantissa: see log2fix_tab()
     int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
     int2     dct_twf[32];    // final DCT stage, lane j = bin j, doubled
-    uint16_t curve[512];     // window multipliers (9 bits, unsigned), window.py:59-115
+    alignas(16) uint16_t curve[512];     // window multipliers (9 bits, unsigned), window.py:59-115
     int16_t  seg_walk[40];   // word address (padded power layout) where lane's walk starts:
                              // segment lane+1, lane 0: segments 0 and 1
     int16_t  seg_close[40];  // closing bin of mel segment g

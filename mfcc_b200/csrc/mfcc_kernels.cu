@@ -206,6 +206,9 @@ struct Smem {
     alignas(8) uint64_t mbar;
 };
 
+// 228 KB of shared memory per SM, 1 KB reserved per resident CTA
+static_assert(sizeof(Smem) + 1024 <= 233472 / CTAS_PER_SM, "the integer kernel must keep CTAS_PER_SM CTAs resident");
+
 __device__ __forceinline__ void issue_tile(const RunParams &p, const TileIter &it, Smem *sm) {
     const Tile g = tile_geo(p, it.ci, it.ti);
     const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
@@ -297,6 +300,8 @@ struct SmemF {
     alignas(16) float xbuf[WARPS_F][NFR_F][mfccf::XWF];
     alignas(8) uint64_t mbar[2];
 };
+
+static_assert(sizeof(SmemF) + 1024 <= 233472 / CTAS_PER_SM_F, "the fp32 kernel must keep CTAS_PER_SM_F CTAs resident");
 
 __device__ __forceinline__ void issue_tile_f(const RunParams &p, const TileIter &it, SmemF *sm, int buf) {
     const Tile g = tile_geo<FT_F>(p, it.ci, it.ti);
@@ -402,6 +407,110 @@ __global__ void k_log2(const uint16_t *m, uint16_t *o, long long total, const De
     // through the same table as the fused kernel (read from global memory here)
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
         o[i] = (uint16_t)log2fix_tab(m[i], tab->logfrac);
+}
+
+// 128-bit forms of the element-wise stages (eight int16 per thread and step); the launcher
+// takes them when the tensors are 16-byte aligned, else the scalar kernels above.
+__device__ __forceinline__ unsigned pk2(int lo, int hi) { return __byte_perm((unsigned)lo, (unsigned)hi, 0x5410); }
+
+__global__ void k_preemph_v(const int16_t *x, int16_t *y, long long n, int prev) {
+    const long long nv = n >> 3;
+    const uint4 *x4 = reinterpret_cast<const uint4 *>(x);
+    uint4 *y4 = reinterpret_cast<uint4 *>(y);
+    for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < nv; j += (long long)gridDim.x * blockDim.x) {
+        const uint4 w = x4[j];
+        int p = j ? (int)x[8 * j - 1] : prev;
+        const unsigned ws[4] = {w.x, w.y, w.z, w.w};
+        unsigned o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int s0 = lo16(ws[q]), s1 = hi16(ws[q]);
+            o[q] = pk2(s0 + (p >> 5) - p, s1 + (s0 >> 5) - s0);
+            p = s1;
+        }
+        y4[j] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    if (blockIdx.x == 0)                                        // ragged tail
+        for (long long i = 8 * nv + threadIdx.x; i < n; i += blockDim.x) {
+            const int p = i ? (int)x[i - 1] : prev;
+            y[i] = (int16_t)((int)x[i] + (p >> 5) - p);
+        }
+}
+
+// hop and nfft are even: a frame starts on a 32-bit word of y
+__global__ void k_frame_v(const int16_t *y, int16_t *fr, long long n, long long n_frames) {
+    const long long total = n_frames * (NFFT / 8);
+    const unsigned *y32 = reinterpret_cast<const unsigned *>(y);
+    uint4 *f4 = reinterpret_cast<uint4 *>(fr);
+    for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < total; j += (long long)gridDim.x * blockDim.x) {
+        const long long k = j / (NFFT / 8), s = k * HOP + 8 * (j - k * (NFFT / 8));
+        unsigned o[4];
+        if (s + 8 <= n) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) o[q] = y32[(s >> 1) + q];
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                o[q] = pk2(s + 2 * q < n ? (int)y[s + 2 * q] : 0, s + 2 * q + 1 < n ? (int)y[s + 2 * q + 1] : 0);
+        }
+        f4[j] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+__global__ void k_window_v(const int16_t *fr, int16_t *w, long long n_frames, const DevTables *tab) {
+    __shared__ uint4 curve4[NFFT / 8];
+    for (int i = threadIdx.x; i < NFFT / 8; i += blockDim.x) curve4[i] = reinterpret_cast<const uint4 *>(tab->curve)[i];
+    __syncthreads();
+    const long long total = n_frames * (NFFT / 8);
+    const uint4 *f4 = reinterpret_cast<const uint4 *>(fr);
+    uint4 *w4 = reinterpret_cast<uint4 *>(w);
+    for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < total; j += (long long)gridDim.x * blockDim.x) {
+        const uint4 a = f4[j], c = curve4[j & (NFFT / 8 - 1)];
+        const unsigned as[4] = {a.x, a.y, a.z, a.w}, cs[4] = {c.x, c.y, c.z, c.w};
+        unsigned o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            o[q] = pk2((lo16(as[q]) * (int)(cs[q] & 0xffffu)) >> 9, (hi16(as[q]) * (int)(cs[q] >> 16)) >> 9);
+        w4[j] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+__global__ void k_power_v(const int16_t *f, uint32_t *pw, long long n_frames) {
+    const long long total = n_frames * (NBINS / 4);
+    const uint4 *f4 = reinterpret_cast<const uint4 *>(f);
+    uint4 *p4 = reinterpret_cast<uint4 *>(pw);
+    for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < total; j += (long long)gridDim.x * blockDim.x) {
+        const uint4 a = f4[j];
+        const unsigned as[4] = {a.x, a.y, a.z, a.w};
+        unsigned o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int re = lo16(as[q]), im = hi16(as[q]);
+            o[q] = ((unsigned)(re * re) + (unsigned)(im * im)) >> 2;
+        }
+        p4[j] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+__global__ void k_log2_v(const uint16_t *m, uint16_t *o, long long total, const DevTables *tab) {
+    __shared__ uint16_t frac[2048];
+    for (int i = threadIdx.x; i < 2048 / 8; i += blockDim.x)
+        reinterpret_cast<uint4 *>(frac)[i] = reinterpret_cast<const uint4 *>(tab->logfrac)[i];
+    __syncthreads();
+    const long long nv = total >> 3;
+    const uint4 *m4 = reinterpret_cast<const uint4 *>(m);
+    uint4 *o4 = reinterpret_cast<uint4 *>(o);
+    for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < nv; j += (long long)gridDim.x * blockDim.x) {
+        const uint4 a = m4[j];
+        const unsigned as[4] = {a.x, a.y, a.z, a.w};
+        unsigned r[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            r[q] = log2fix_tab(as[q] & 0xffffu, frac) | (log2fix_tab(as[q] >> 16, frac) << 16);
+        o4[j] = make_uint4(r[0], r[1], r[2], r[3]);
+    }
+    if (blockIdx.x == 0)
+        for (long long i = 8 * nv + threadIdx.x; i < total; i += blockDim.x) o[i] = (uint16_t)log2fix_tab(m[i], frac);
 }
 
 struct StageSmem {
@@ -1006,21 +1115,29 @@ int mfcc_b200_stage(void *handle, int32_t stage, const void *d_in, void *d_out, 
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int nf = h->cfg.nfilters;
     const int B = 256;
+    const uintptr_t ai = reinterpret_cast<uintptr_t>(d_in), ao = reinterpret_cast<uintptr_t>(d_out);
+    const bool v16 = ((ai | ao) & 15) == 0;                     // both tensors take 128-bit accesses
     switch (stage) {
     case MFCC_B200_STAGE_PREEMPH:
-        k_preemph<<<grid_1d(n, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, prev);
+        if (v16 && n >= 8) k_preemph_v<<<grid_1d(n / 8, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, prev);
+        else k_preemph<<<grid_1d(n, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, prev);
         break;
     case MFCC_B200_STAGE_FRAME:
-        k_frame<<<grid_1d(n_frames * NFFT, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, n_frames);
+        if ((ai & 3) == 0 && (ao & 15) == 0)
+            k_frame_v<<<grid_1d(n_frames * (NFFT / 8), B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, n_frames);
+        else k_frame<<<grid_1d(n_frames * NFFT, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, n_frames);
         break;
     case MFCC_B200_STAGE_WINDOW:
-        k_window<<<grid_1d(n * NFFT, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, h->d_tab);
+        if (v16) k_window_v<<<grid_1d(n * (NFFT / 8), B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, h->d_tab);
+        else k_window<<<grid_1d(n * NFFT, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (int16_t *)d_out, n, h->d_tab);
         break;
     case MFCC_B200_STAGE_POWER:
-        k_power<<<grid_1d(n * NBINS, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (uint32_t *)d_out, n);
+        if (v16) k_power_v<<<grid_1d(n * (NBINS / 4), B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (uint32_t *)d_out, n);
+        else k_power<<<grid_1d(n * NBINS, B, h->sm_count), B, 0, s>>>((const int16_t *)d_in, (uint32_t *)d_out, n);
         break;
     case MFCC_B200_STAGE_LOG2:
-        k_log2<<<grid_1d(n * nf, B, h->sm_count), B, 0, s>>>((const uint16_t *)d_in, (uint16_t *)d_out, n * nf, h->d_tab);
+        if (v16 && n * nf >= 8) k_log2_v<<<grid_1d(n * nf / 8, B, h->sm_count), B, 0, s>>>((const uint16_t *)d_in, (uint16_t *)d_out, n * nf, h->d_tab);
+        else k_log2<<<grid_1d(n * nf, B, h->sm_count), B, 0, s>>>((const uint16_t *)d_in, (uint16_t *)d_out, n * nf, h->d_tab);
         break;
     default: {
         const int grid = grid_1d(n, WARPS, h->sm_count);

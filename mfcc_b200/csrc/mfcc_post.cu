@@ -129,12 +129,57 @@ __global__ void k_frame_general(const int16_t *y, int16_t *fr, long long n, long
     }
 }
 
+// 128-bit form for even windowlen / stepsize, nfft a multiple of 8, y on a 32-bit and fr on a
+// 16-byte boundary: eight outputs per thread and step, sample pairs as 32-bit words
+__global__ void k_frame_general_v(const int16_t *y, int16_t *fr, long long n, long long n_frames, int windowlen,
+                                  int stepsize, int nfft) {
+    const int vpf = nfft >> 3;
+    const long long total = n_frames * vpf;
+    const unsigned *y32 = reinterpret_cast<const unsigned *>(y);
+    uint4 *f4 = reinterpret_cast<uint4 *>(fr);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long k = i / vpf;
+        const int j = (int)(i - k * vpf) << 3;
+        const long long s = k * stepsize + j;
+        unsigned o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int jj = j + 2 * q;
+            const long long ss = s + 2 * q;
+            if (jj + 1 < windowlen && ss + 1 < n) o[q] = y32[ss >> 1];
+            else {
+                const unsigned lo = (jj < windowlen && ss < n) ? (unsigned short)y[ss] : 0u;
+                const unsigned hi = (jj + 1 < windowlen && ss + 1 < n) ? (unsigned short)y[ss + 1] : 0u;
+                o[q] = lo | (hi << 16);
+            }
+        }
+        f4[i] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 // PowerSpectrum(width=16, width_output), mfcc/core/pow2.py:32, :64: the 32-bit sum of the two
 // squares (it wraps for re = im = -32768), top width_output bits
 __global__ void k_power_general(const int16_t *f, uint32_t *pw, long long total, int shift) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int re = f[2 * i], im = f[2 * i + 1];
         pw[i] = ((unsigned)(re * re) + (unsigned)(im * im)) >> shift;
+    }
+}
+
+// four bins per thread and step (128-bit loads and stores); the launcher adds the scalar tail
+__global__ void k_power_general_v(const int16_t *f, uint32_t *pw, long long total4, int shift) {
+    const uint4 *f4 = reinterpret_cast<const uint4 *>(f);
+    uint4 *p4 = reinterpret_cast<uint4 *>(pw);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4; i += (long long)gridDim.x * blockDim.x) {
+        const uint4 a = f4[i];
+        const unsigned as[4] = {a.x, a.y, a.z, a.w};
+        unsigned o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int re = (int)(short)(as[q] & 0xffffu), im = (int)as[q] >> 16;
+            o[q] = ((unsigned)(re * re) + (unsigned)(im * im)) >> shift;
+        }
+        p4[i] = make_uint4(o[0], o[1], o[2], o[3]);
     }
 }
 
@@ -293,8 +338,14 @@ int mfcc_b200_frame(const int16_t *d_in, int16_t *d_out, int64_t n, int64_t n_fr
     if (windowlen < 1 || stepsize < 1 || nfft < windowlen) return fail_ext(MFCC_B200_EINVAL, "need 1 <= windowlen <= nfft, stepsize >= 1");
     if (n_frames == 0) return MFCC_B200_OK;
     if (!d_out || (n > 0 && !d_in)) return fail_ext(MFCC_B200_EINVAL, "null buffer");
-    k_frame_general<<<grid_for(n_frames * nfft, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n, n_frames, windowlen,
-                                                                                    stepsize, nfft);
+    const bool vec = !(windowlen & 1) && !(stepsize & 1) && !(nfft & 7) &&
+                     !(reinterpret_cast<uintptr_t>(d_in) & 3) && !(reinterpret_cast<uintptr_t>(d_out) & 15);
+    if (vec)
+        k_frame_general_v<<<grid_for(n_frames * (nfft >> 3), 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n, n_frames,
+                                                                                                 windowlen, stepsize, nfft);
+    else
+        k_frame_general<<<grid_for(n_frames * nfft, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n, n_frames, windowlen,
+                                                                                        stepsize, nfft);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
 }
@@ -348,7 +399,12 @@ int mfcc_b200_power(const int16_t *d_in, uint32_t *d_out, int64_t n_bins, int32_
     if (n_bins < 0 || width_output < 1 || width_output > 32) return fail_ext(MFCC_B200_EINVAL, "need n_bins >= 0 and 1 <= width_output <= 32");
     if (n_bins == 0) return MFCC_B200_OK;
     if (!d_in || !d_out) return fail_ext(MFCC_B200_EINVAL, "null buffer");
-    k_power_general<<<grid_for(n_bins, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n_bins, 32 - width_output);
+    const bool vec = !((reinterpret_cast<uintptr_t>(d_in) | reinterpret_cast<uintptr_t>(d_out)) & 15) && n_bins >= 4;
+    const int64_t nv = vec ? (n_bins & ~(int64_t)3) : 0;               // bins done four at a time
+    if (nv) k_power_general_v<<<grid_for(nv / 4, 256), 256, 0, (cudaStream_t)stream>>>(d_in, d_out, nv / 4, 32 - width_output);
+    if (n_bins > nv)
+        k_power_general<<<grid_for(n_bins - nv, 256), 256, 0, (cudaStream_t)stream>>>(d_in + 2 * nv, d_out + nv, n_bins - nv,
+                                                                                      32 - width_output);
     POST_LAUNCH_CHECK();
     return MFCC_B200_OK;
 }
