@@ -26,9 +26,23 @@ namespace {
 
 constexpr int WARPS   = 8;
 constexpr int THREADS = WARPS * 32;
-constexpr int FT      = 24;                                        // frames per tile
-constexpr int RAWN    = ((HOP * (FT - 1) + NFFT + 15) + 7) & ~7;   // samples per tile buffer
-constexpr int CTAS_PER_SM = 4;
+// CTA shapes of the fused integer kernel.  Large batches take 72-frame tiles on 2 CTAs x 12 warps
+// (72 registers per thread instead of 64 and six frames per warp between block barriers: fewer
+// instructions per frame and a smaller tile prologue per frame); small inputs keep 24-frame tiles
+// on 4 CTAs x 8 warps, which cut a short clip into enough tiles to fill the machine.
+template <int W, int F, int C>
+struct IntShape {
+    static constexpr int WARPS = W, THREADS = W * 32, FT = F, CTAS = C;
+    static constexpr int RAWN = ((HOP * (F - 1) + NFFT + 15) + 7) & ~7;   // samples per tile buffer
+};
+#ifndef MFCC_INT_BIG_W
+#define MFCC_INT_BIG_W 12
+#endif
+#ifndef MFCC_INT_BIG_FT
+#define MFCC_INT_BIG_FT 72
+#endif
+using ShapeBig = IntShape<MFCC_INT_BIG_W, MFCC_INT_BIG_FT, 2>;
+using ShapeSmall = IntShape<8, 24, 4>;
 // the fp32 kernel has its own CTA shape (it is bound by shared-memory latency, not by issue)
 #ifndef MFCC_F32_WARPS
 #define MFCC_F32_WARPS 8
@@ -109,10 +123,11 @@ struct Tile {
 // tile `ti` of clip `ci` (the persistent kernels step (ci, ti) by the grid size without dividing).
 // A tile starts FT * HOP samples after the previous one, a multiple of 8: raw[0] is always the
 // sample 8 before the tile's first frame, so every bulk copy is 16-byte aligned on both sides.
-static_assert((FT * HOP) % 8 == 0 && (FT_F * HOP) % 8 == 0, "tiles must start on 16-byte boundaries of the clip");
+static_assert((ShapeBig::FT * HOP) % 8 == 0 && (ShapeSmall::FT * HOP) % 8 == 0 && (FT_F * HOP) % 8 == 0,
+              "tiles must start on 16-byte boundaries of the clip");
 static_assert(FT_F % (NFR_F * WARPS_F) == 0, "every frame a warp touches must lie inside the tile buffer");
 constexpr int OFF0 = 8;                                      // raw[OFF0] = first sample of the tile's first frame
-template <int FTT = FT>
+template <int FTT>
 __device__ __forceinline__ Tile tile_geo(const RunParams &p, long long ci, int ti) {
     Tile g;
     g.ci = ci;
@@ -198,19 +213,22 @@ __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, c
 }
 
 // ------------------------------------------------------------------ fused kernel
+template <class SH>
 struct Smem {
     DevTables tab;
-    alignas(16) int16_t raw[RAWN];
-    alignas(16) int16_t pre[RAWN];
-    alignas(16) unsigned xbuf[WARPS][XW];
+    alignas(16) int16_t raw[SH::RAWN];
+    alignas(16) int16_t pre[SH::RAWN];
+    alignas(16) unsigned xbuf[SH::WARPS][XW];
     alignas(8) uint64_t mbar;
 };
 
 // 228 KB of shared memory per SM, 1 KB reserved per resident CTA
-static_assert(sizeof(Smem) + 1024 <= 233472 / CTAS_PER_SM, "the integer kernel must keep CTAS_PER_SM CTAs resident");
+static_assert(sizeof(Smem<ShapeBig>) + 1024 <= 233472 / ShapeBig::CTAS && sizeof(Smem<ShapeSmall>) + 1024 <= 233472 / ShapeSmall::CTAS,
+              "the integer kernel must keep its CTAs resident");
 
-__device__ __forceinline__ void issue_tile(const RunParams &p, const TileIter &it, Smem *sm) {
-    const Tile g = tile_geo(p, it.ci, it.ti);
+template <class SH>
+__device__ __forceinline__ void issue_tile(const RunParams &p, const TileIter &it, Smem<SH> *sm) {
+    const Tile g = tile_geo<SH::FT>(p, it.ci, it.ti);
     const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
     if (bytes) {
         mbar_arrive_expect_tx(&sm->mbar, bytes);
@@ -220,17 +238,17 @@ __device__ __forceinline__ void issue_tile(const RunParams &p, const TileIter &i
     }
 }
 
-template <int NF, bool TAPS>
-__global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const RunParams p)
+template <int NF, bool TAPS, class SH>
+__global__ void __launch_bounds__(SH::THREADS, SH::CTAS) mfcc_int_fused(const RunParams p)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem *sm = reinterpret_cast<Smem *>(smem_raw);
+    Smem<SH> *sm = reinterpret_cast<Smem<SH> *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     {   // tables: global -> shared, once per CTA
         const int4 *src = reinterpret_cast<const int4 *>(p.tab);
         int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
-        for (int i = tid; i < (int)(sizeof(DevTables) / 16); i += THREADS) dst[i] = src[i];
+        for (int i = tid; i < (int)(sizeof(DevTables) / 16); i += SH::THREADS) dst[i] = src[i];
     }
     if (tid == 0) mbar_init(&sm->mbar, 1);
     __syncthreads();
@@ -241,12 +259,12 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
     uint32_t phase = 0;
 
     while (it.tile < p.n_tiles) {
-        const Tile g = tile_geo(p, it.ci, it.ti);
+        const Tile g = tile_geo<SH::FT>(p, it.ci, it.ti);
         it.next();
         // samples the bulk copy does not cover: before the clip (zeros), the ragged
         // tail and everything past the end (zeros, software/main.c:135-144)
-        for (int j = tid; j < g.lo; j += THREADS) sm->raw[j] = 0;
-        for (int j = g.hi + tid; j < g.len; j += THREADS) {
+        for (int j = tid; j < g.lo; j += SH::THREADS) sm->raw[j] = 0;
+        for (int j = g.hi + tid; j < g.len; j += SH::THREADS) {
             const long long s = g.a0 + j;
             sm->raw[j] = (s >= 0 && s < p.n_samples) ? g.clip[s] : (int16_t)0;
         }
@@ -262,7 +280,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
             const unsigned *r32 = reinterpret_cast<const unsigned *>(sm->raw);
             uint4 *p128 = reinterpret_cast<uint4 *>(sm->pre);
             const int nq = (g.len + 7) >> 3;
-            for (int i = tid; i < nq; i += THREADS) {
+            for (int i = tid; i < nq; i += SH::THREADS) {
                 const uint4 w = r128[i];
                 int sp = i ? hi16(r32[4 * i - 1]) : 0;
                 const unsigned ws[4] = {w.x, w.y, w.z, w.w};
@@ -282,7 +300,7 @@ __global__ void __launch_bounds__(THREADS, CTAS_PER_SM) mfcc_int_fused(const Run
         // raw[] is free again: prefetch the next tile while this one is computed
         if (tid == 0 && it.tile < p.n_tiles) issue_tile(p, it, sm);
         int16_t *otile = static_cast<int16_t *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
-        for (int fl = warp; fl < g.nf; fl += WARPS)
+        for (int fl = warp; fl < g.nf; fl += SH::WARPS)
             frame_warp<NF, TAPS>(sm->pre + OFF0 + HOP * fl, sm->xbuf[warp], &sm->tab, lane,
                                  otile + fl * p.nceptrums, p.nceptrums, p.taps, g.f0 + fl);
         __syncthreads();
@@ -966,10 +984,12 @@ int mfcc_b200_create(const mfcc_b200_cfg *cfg, void **handle)
         delete h;
         return fail(MFCC_B200_ECUDA, std::string("mfcc_b200_create: ") + cudaGetErrorString(e));
     }
-    rc = set_smem(mfcc_int_fused<32, false>, sizeof(Smem));
-    if (!rc) rc = set_smem(mfcc_int_fused<16, false>, sizeof(Smem));
-    if (!rc) rc = set_smem(mfcc_int_fused<32, true>, sizeof(Smem));
-    if (!rc) rc = set_smem(mfcc_int_fused<16, true>, sizeof(Smem));
+    rc = set_smem(mfcc_int_fused<32, false, ShapeBig>, sizeof(Smem<ShapeBig>));
+    if (!rc) rc = set_smem(mfcc_int_fused<16, false, ShapeBig>, sizeof(Smem<ShapeBig>));
+    if (!rc) rc = set_smem(mfcc_int_fused<32, false, ShapeSmall>, sizeof(Smem<ShapeSmall>));
+    if (!rc) rc = set_smem(mfcc_int_fused<16, false, ShapeSmall>, sizeof(Smem<ShapeSmall>));
+    if (!rc) rc = set_smem(mfcc_int_fused<32, true, ShapeSmall>, sizeof(Smem<ShapeSmall>));
+    if (!rc) rc = set_smem(mfcc_int_fused<16, true, ShapeSmall>, sizeof(Smem<ShapeSmall>));
     if (!rc) rc = set_smem(mfcc_int_step<32>, sizeof(StepSmem));
     if (!rc) rc = set_smem(mfcc_int_step<16>, sizeof(StepSmem));
     if (!rc) rc = set_smem(k_warp_stage<MFCC_B200_STAGE_FFT, 32>, sizeof(StageSmem));
@@ -1023,12 +1043,15 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
     p.out = d_out; p.out_clip_stride = out_clip_stride;
     p.tab = h->d_tab; p.ftab = h->d_ftab; p.nceptrums = h->cfg.nceptrums;
     const bool f32 = h->cfg.mode == MFCC_B200_MODE_FP32;
-    const int ft = f32 ? FT_F : FT;
+    // integer mode: the large shape once the batch fills the machine four times over with its tiles
+    const long long big_tiles = ((n_frames + ShapeBig::FT - 1) / ShapeBig::FT) * n_clips;
+    const bool big = !f32 && !taps && big_tiles >= 4LL * h->sm_count * ShapeBig::CTAS;
+    const int ft = f32 ? FT_F : big ? ShapeBig::FT : ShapeSmall::FT;
     p.tiles_per_clip = (int)((n_frames + ft - 1) / ft);
     p.n_tiles = (long long)p.tiles_per_clip * n_clips;
     p.aligned = ((reinterpret_cast<uintptr_t>(d_x) & 15) == 0) && (n_clips == 1 || (clip_stride % 8) == 0);
     if (taps) p.taps = *taps;
-    long long grid = (long long)h->sm_count * (f32 ? CTAS_PER_SM_F : CTAS_PER_SM);
+    long long grid = (long long)h->sm_count * (f32 ? CTAS_PER_SM_F : big ? ShapeBig::CTAS : ShapeSmall::CTAS);
     if (grid > p.n_tiles) grid = p.n_tiles;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (f32) {
@@ -1036,10 +1059,14 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
         else                       mfcc_f32_fused<16><<<(unsigned)grid, THREADS_F, sizeof(SmemF), s>>>(p);
     } else {
         const bool nf32 = h->cfg.nfilters == 32;
-        if (taps && nf32)  mfcc_int_fused<32, true><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
-        else if (taps)     mfcc_int_fused<16, true><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
-        else if (nf32)     mfcc_int_fused<32, false><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
-        else               mfcc_int_fused<16, false><<<(unsigned)grid, THREADS, sizeof(Smem), s>>>(p);
+        using SB = ShapeBig;
+        using SS = ShapeSmall;
+        if (taps && nf32)  mfcc_int_fused<32, true, SS><<<(unsigned)grid, SS::THREADS, sizeof(Smem<SS>), s>>>(p);
+        else if (taps)     mfcc_int_fused<16, true, SS><<<(unsigned)grid, SS::THREADS, sizeof(Smem<SS>), s>>>(p);
+        else if (big && nf32) mfcc_int_fused<32, false, SB><<<(unsigned)grid, SB::THREADS, sizeof(Smem<SB>), s>>>(p);
+        else if (big)      mfcc_int_fused<16, false, SB><<<(unsigned)grid, SB::THREADS, sizeof(Smem<SB>), s>>>(p);
+        else if (nf32)     mfcc_int_fused<32, false, SS><<<(unsigned)grid, SS::THREADS, sizeof(Smem<SS>), s>>>(p);
+        else               mfcc_int_fused<16, false, SS><<<(unsigned)grid, SS::THREADS, sizeof(Smem<SS>), s>>>(p);
     }
     g_launches.fetch_add(1);
     CUDA_TRY(cudaGetLastError());

@@ -67,7 +67,7 @@ def main():
                 name = r[4].replace("void ", "").replace("<unnamed>::", "").split("(")[0]
                 a = agg.setdefault(name, [0, 0.0])
                 a[0] += 1
-                if "mfcc_int_fused" in name and r[8].replace(" ", "").startswith("(592,"):
+                if "mfcc_int_fused" in name and r[8].replace(" ", "").startswith(("(592,", "(296,")):
                     full.append(float(r[14].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0}.get(r[13], 1e-6))
                 a[1] += float(r[14].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0}.get(r[13], 1e-6)
         tot = sum(v[1] for v in agg.values())
@@ -78,7 +78,7 @@ def main():
             for name, (n, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
                 f.write("%-40s %8d %12.3f %7.1f%%\n" % (name, n, ms, 100 * ms / tot))
             big = sorted(full, reverse=True)[:5]
-            f.write("# the timed step of bench.py is ONE launch of mfcc_int_fused<32, 0> over 10 000 clips (100 %% of the "
+            f.write("# the timed step of bench.py is ONE launch of mfcc_int_fused<32, 0, ...> over 10 000 clips (100 %% of the "
                     "step);\n# its full-size launches here took %s ms\n" % ", ".join("%.2f" % v for v in big))
     pb = os.path.join(G, "%s_pipe_bench.jsonl" % tag)
     if os.path.exists(pb):

@@ -119,6 +119,22 @@ def test_many_clips_full_length(ops, RC):
     assert (tp["mel"] > 0).any()
 
 
+def test_large_batch_takes_the_72_frame_tiles(ops, RC):
+    """Batches that fill the machine several times over run the 2 x 12-warp shape with 72-frame
+    tiles (24 clips x 79 tiles here); ragged length, so the last tile of every clip is partial
+    and the tail is read by plain loads."""
+    m = ops[(32, 32)]
+    cfg = RC.RefConfig()
+    import bench
+    x = bench.synth_clips(24, 960000, torch.device("cuda"), first_clip=0)[:, :960000 - 37].contiguous()
+    got = m(x).cpu().numpy()
+    want = RC.run(cfg, x.cpu().numpy(), threads=RC.max_threads())
+    assert got.shape == want.shape and np.array_equal(got, want)
+    # zero-extended frame count of the host protocol on the same batch
+    k = m.cfg.num_frames_host(x.shape[1])
+    assert np.array_equal(m(x, n_frames=k).cpu().numpy(), RC.run(cfg, x.cpu().numpy(), n_frames=k, threads=RC.max_threads()))
+
+
 def test_run_host_equals_device_path(ops, RC):
     m = ops[(32, 16)]
     cfg = RC.RefConfig(nfilters=32, nceptrums=16)
