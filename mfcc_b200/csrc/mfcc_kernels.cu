@@ -2,11 +2,13 @@
 //
 // mfcc_int_fused: the whole chain Preemph -> Frame -> WindowHamming -> FftStream ->
 // PowerSpectrum -> FilterBank -> Log2Fix -> DCTStream -> Discard of
-// /root/reference/mfcc/core/mfcc.py:90-104 in one launch.  A CTA of 8 warps walks
-// tiles of 32 consecutive frames of one clip: the tile's int16 sample run arrives in
+// /root/reference/mfcc/core/mfcc.py:90-104 in one launch.  A persistent CTA (12 warps on
+// 72-frame tiles for large batches, 8 warps on 24-frame tiles otherwise: IntShape below) walks
+// tiles of consecutive frames of one clip: the tile's int16 sample run arrives in
 // shared memory through one TMA bulk copy (prefetched while the previous tile is
 // computed), is pre-emphasised once, and each warp then turns frames into cepstra;
 // only the cepstra go back to HBM.
+// mfcc_f32_fused: the float prototype of the same chain, two frames per warp at a time.
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
