@@ -179,10 +179,15 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
                        ((hop & 1) == 0);
 
     const long long total = (long long)n_clips * n_frames;
-    for (long long item = (long long)blockIdx.x * LR_WARPS + warp; item < total; item += (long long)gridDim.x * LR_WARPS) {
-        const int clip = (int)(item / n_frames);
-        const long long f = item - (long long)clip * n_frames;
-        const int16_t *x = d_x + (long long)clip * clip_stride;
+    // (clip, frame) of the warp's item, stepped by the grid's stride without a division per frame
+    const long long stride = (long long)gridDim.x * LR_WARPS;
+    const long long dq = stride / n_frames, dr = stride - dq * n_frames;
+    long long item = (long long)blockIdx.x * LR_WARPS + warp;
+    long long clip_l = item / n_frames, f = item - clip_l * n_frames;
+    for (; item < total; item += stride, clip_l += dq, f += dr) {
+        if (f >= n_frames) { f -= n_frames; ++clip_l; }
+        const int clip = (int)clip_l;
+        const int16_t *x = d_x + clip_l * clip_stride;
         const long long s0 = f * hop - (center ? LR_HALF : 0);
 
         // lane L takes z[L + 32 i], z[n] = (y[2n] w[2n], y[2n+1] w[2n+1]): coalesced 128-byte rows
