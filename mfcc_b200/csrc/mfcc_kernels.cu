@@ -1046,8 +1046,12 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
     p.tab = h->d_tab; p.ftab = h->d_ftab; p.nceptrums = h->cfg.nceptrums;
     const bool f32 = h->cfg.mode == MFCC_B200_MODE_FP32;
     // integer mode: the large shape once the batch fills the machine four times over with its tiles
-    const long long big_tiles = ((n_frames + ShapeBig::FT - 1) / ShapeBig::FT) * n_clips;
-    const bool big = !f32 && !taps && big_tiles >= 4LL * h->sm_count * ShapeBig::CTAS;
+    // (and its partly empty last tile per clip does not cost more than the shape gains)
+    const long long tpc_big = (n_frames + ShapeBig::FT - 1) / ShapeBig::FT;
+    const long long tpc_small = (n_frames + ShapeSmall::FT - 1) / ShapeSmall::FT;
+    const long long big_tiles = tpc_big * n_clips;
+    const bool big = !f32 && !taps && big_tiles >= 4LL * h->sm_count * ShapeBig::CTAS &&
+                     tpc_big * ShapeBig::FT * 100 <= tpc_small * ShapeSmall::FT * 105;
     const int ft = f32 ? FT_F : big ? ShapeBig::FT : ShapeSmall::FT;
     p.tiles_per_clip = (int)((n_frames + ft - 1) / ft);
     p.n_tiles = (long long)p.tiles_per_clip * n_clips;

@@ -146,6 +146,21 @@ def test_run_host_equals_device_path(ops, RC):
     assert np.array_equal(m.run_host(torch.from_numpy(x)).numpy(), want)     # pageable too
 
 
+@pytest.mark.parametrize("frames", [100, 200])
+def test_many_short_clips(ops, RC, frames):
+    """2000 short clips in one launch: 200 frames each take the 72-frame tiles (three per clip,
+    the last one partial), 100 frames each stay on the 24-frame tiles (the large shape would
+    leave its second tile mostly empty)."""
+    m = ops[(32, 32)]
+    cfg = RC.RefConfig()
+    rng = np.random.default_rng(frames)
+    n = 512 + 170 * (frames - 1) + 5
+    x = rng.integers(-32768, 32768, (2000, n)).astype(np.int16)
+    got = m(dev(x)).cpu().numpy()
+    want = RC.run(cfg, x, threads=RC.max_threads())
+    assert got.shape == (2000, frames, 32) and np.array_equal(got, want)
+
+
 # ---- size-independent properties at full scale ---------------------------------------
 def test_properties_at_scale(ops):
     m = ops[(32, 32)]
