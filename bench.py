@@ -119,9 +119,11 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_oracle_rate(n_clips, threads, repeats=1):
-    """Frames/s of the C oracle (oracle/mfcc_ref.c, the CPU restatement of the RTL) on
-    `n_clips` clips of the same workload.  This is the only place bench.py runs oracle/."""
+def cpu_oracle_rate(n_clips, threads, repeats=1, fast=True):
+    """Frames/s of the CPU restatement of the RTL on `n_clips` clips of the same workload:
+    fast=True is oracle/mfcc_ref_fast.c built here with gcc -O3 -march=native -fopenmp (the
+    timed baseline, bit-identical to the checker: tests/test_oracle.py), fast=False the
+    checker oracle/mfcc_ref.c (-O2).  This is the only place bench.py runs oracle/."""
     import numpy as np
     import torch
     from oracle import ref_c as RC
@@ -131,7 +133,7 @@ def cpu_oracle_rate(n_clips, threads, repeats=1):
     best = None
     for _ in range(repeats):
         t0 = time.perf_counter()
-        RC.run(cfg, x, threads=threads)
+        RC.run(cfg, x, threads=threads, fast=fast)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
     return frames / best, frames, best
@@ -140,8 +142,9 @@ def cpu_oracle_rate(n_clips, threads, repeats=1):
 def run_reference(args, rank, world):
     """--impl reference: the reference's integer pipeline on the host cores.  The
     reference hot path is nMigen RTL and cannot run here (no nmigen, no simulator), so
-    this arm times the CPU restatement of it (oracle/mfcc_ref.c, "port") with all host
-    threads, on a bounded sample of the same workload per step."""
+    this arm times the CPU restatement of it ("port": oracle/mfcc_ref_fast.c, gcc -O3
+    -march=native -fopenmp, built on this machine, bit-identical to the checker) with all
+    host threads, on a bounded sample of the same workload per step."""
     if rank != 0:
         return
     from oracle import ref_c as RC
@@ -152,11 +155,12 @@ def run_reference(args, rank, world):
     cfg = RC.RefConfig(nfilters=NFILT, nceptrums=NCEP)
     x = synth_clips(n_clips, N_SAMPLES, torch.device("cpu")).numpy()
     frames = n_clips * cfg.num_frames(N_SAMPLES)
+    RC.build_fast()
     for _ in range(args.warmup):
-        RC.run(cfg, x[: max(1, n_clips // 8)], threads=threads)
+        RC.run(cfg, x[: max(1, n_clips // 8)], threads=threads, fast=True)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        RC.run(cfg, x, threads=threads)
+        RC.run(cfg, x, threads=threads, fast=True)
     dt = (time.perf_counter() - t0) / args.steps
     v = frames / dt
     sample = "%d clips x 60 s (%d frames) per step" % (n_clips, frames)
@@ -167,7 +171,8 @@ def run_reference(args, rank, world):
         "data": "synthetic", "audio_sec_per_sec": v * 170 / 16000,
         "config": {"workload": "C2: synthetic 60 s int16 clips, 512/170 frames, 32 mel, 32 cepstra, "
                                "integer mode (bounded sample)", "sample": sample},
-        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample,
+                         "build_flags": "gcc " + RC.FAST_FLAGS, "source": "oracle/mfcc_ref_fast.c"},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
@@ -256,6 +261,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--clips", type=int, default=N_CLIPS, help="clips per GPU (default: configs[1])")
     ap.add_argument("--e2e-clips", type=int, default=2048)
+    ap.add_argument("--e2e-chunk-mb", type=float, default=None, help="run_host chunk size (MiB of samples)")
+    ap.add_argument("--e2e-slots", type=int, default=None, help="run_host chunks in flight (2..8)")
+    ap.add_argument("--e2e-wc", action="store_true", help="write-combined pinned sample buffer")
+    ap.add_argument("--e2e-sweep", action="store_true",
+                    help="also time run_host over a grid of chunk sizes / slots (extra key e2e.sweep)")
+    ap.add_argument("--no-c4", action="store_true", help="skip the C4 (10^6 audio-seconds, strong scaling) leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-numa", action="store_true",
                     help="do not pin the process to the GPU's local CPU cores (NUMA node)")
@@ -320,28 +331,114 @@ def main():
     value = frames_rank * world * args.steps / t_max
 
     # ---- end to end: pinned host buffers through the C-ABI host entry point
+    from mfcc_b200.mfcc import pinned_empty
     ne = min(args.e2e_clips, args.clips)
-    xh = torch.empty((ne, N_SAMPLES), dtype=torch.int16).pin_memory()
+    xh = pinned_empty((ne, N_SAMPLES), torch.int16, write_combined=args.e2e_wc)
     xh.copy_(x[:ne])
-    oh = torch.empty((ne, K, NCEP), dtype=torch.int16).pin_memory()
+    oh = pinned_empty((ne, K, NCEP), torch.int16)
     e_steps = max(1, min(args.steps, 5))
-    op.run_host(xh, out=oh)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e_steps):
-        op.run_host(xh, out=oh)
-    torch.cuda.synchronize()
-    te = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = ne * K * world * e_steps / float(te.item())
+    op.host_config(args.e2e_chunk_mb, args.e2e_slots)
+
+    def timed_host(fn, steps):
+        """Wall time of `steps` synchronous calls, max over ranks (fn returns with the device idle)."""
+        fn()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            fn()
+        torch.cuda.synchronize()
+        t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    t_e2e = timed_host(lambda: op.run_host(xh, out=oh), e_steps)
+    e2e_value = ne * K * world / t_e2e
     e2e_ok = bool(torch.equal(oh.to(dev), out[:ne]))
+
+    # ---- copy-only ceiling of the same end-to-end step: the same pinned buffers and byte
+    # counts, plain cudaMemcpyAsync host->device and device->host on two streams, no kernel
+    cs_in, cs_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    xd, od = x[:ne], out[:ne]                       # same contents as xh / oh: nothing changes
+
+    def copy_both(h2d=True, d2h=True):
+        if h2d:
+            with torch.cuda.stream(cs_in):
+                xd.copy_(xh, non_blocking=True)
+        if d2h:
+            with torch.cuda.stream(cs_out):
+                oh.copy_(od, non_blocking=True)
+        cs_in.synchronize()
+        cs_out.synchronize()
+
+    h2d_b, d2h_b = ne * N_SAMPLES * 2, ne * K * NCEP * 2
+    t_both = timed_host(copy_both, e_steps)
+    t_h2d = timed_host(lambda: copy_both(d2h=False), e_steps)
+    t_d2h = timed_host(lambda: copy_both(h2d=False), e_steps)
+    copy_ceiling = {"value": ne * K * world / t_both, "unit": "frames/s",
+                    "what": "same pinned buffers and bytes as e2e, cudaMemcpyAsync H2D + D2H on two streams, "
+                            "no kernel; all ranks at once, max over ranks",
+                    "ms_per_step": t_both * 1e3,
+                    "h2d_gbs_all_gpus": h2d_b * world / t_both / 1e9, "d2h_gbs_all_gpus": d2h_b * world / t_both / 1e9,
+                    "h2d_alone_gbs_all_gpus": h2d_b * world / t_h2d / 1e9,
+                    "d2h_alone_gbs_all_gpus": d2h_b * world / t_d2h / 1e9,
+                    "e2e_over_ceiling": e2e_value / (ne * K * world / t_both)}
+    e2e_sweep = None
+    if args.e2e_sweep:
+        e2e_sweep = []
+        for mb, sl in ((8, 4), (16, 4), (32, 2), (32, 3), (32, 4), (32, 8), (64, 4), (128, 4), (256, 3)):
+            op.host_config(mb, sl)
+            ts = timed_host(lambda: op.run_host(xh, out=oh), max(2, e_steps // 2))
+            e2e_sweep.append({"chunk_mb": mb, "slots": sl, "value": ne * K * world / ts})
+        op.host_config(args.e2e_chunk_mb or 32, args.e2e_slots or 4)
+    del xd, od, xh, oh
+
+    # ---- C4 (BASELINE.json configs[3]): 10^6 audio-seconds = 16 667 clips of 60 s, rank r of G
+    # owns clips r::G (strong scaling: the total is fixed, the per-GPU share shrinks with G)
+    c4 = None
+    if not args.no_c4:
+        C4_CLIPS = 16667
+        mine = list(range(rank, C4_CLIPS, world))
+        n4 = len(mine)
+        if n4 <= args.clips:
+            x4, o4 = x[:n4], out[:n4]               # the device never looks at the seed: reuse the resident clips
+        else:
+            x4 = torch.empty((n4, N_SAMPLES), dtype=torch.int16, device=dev)
+            x4[:args.clips] = x
+            synth_clips(n4 - args.clips, N_SAMPLES, dev, first_clip=(rank + world) * args.clips, out=x4[args.clips:])
+            o4 = torch.empty((n4, K, NCEP), dtype=torch.int16, device=dev)
+        c_steps = max(3, min(args.steps, 10))
+        for _ in range(3):
+            op(x4, out=o4)
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(c_steps):
+            op(x4, out=o4)
+        c1.record()
+        barrier()
+        t4 = torch.tensor([c0.elapsed_time(c1) * 1e-3 / c_steps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t4, op=dist.ReduceOp.MAX)
+        t4 = float(t4.item())
+        c4 = {"workload": "C4: 10^6 audio-seconds = %d clips x 60 s (%d frames) over %d GPU(s), rank r owns clips r::G"
+                          % (C4_CLIPS, C4_CLIPS * K, world),
+              "scaling": "strong", "clips_this_rank": n4, "steps": c_steps, "ms_per_pass": t4 * 1e3,
+              "value": C4_CLIPS * K / t4, "unit": "frames/s", "audio_sec_per_sec": C4_CLIPS * 60.0 / t4}
+        try:
+            ref1 = json.load(open(os.path.join(ROOT, "profiles", "r02_c4_n1.json")))["ms_per_pass"]
+            c4["efficiency_vs_recorded_n1"] = ref1 / (t4 * 1e3) / world
+            c4["recorded_n1_ms_per_pass"] = ref1
+        except Exception:
+            pass
+        if n4 > args.clips:
+            del x4, o4
+            torch.cuda.empty_cache()
 
     extras = {}
     if world == 1 and not args.no_extras:
         # Extra legs of the N=1 line.  Each is guarded: a failure is recorded in the line
         # and can never cost the headline numbers measured above.
-        del xh, oh
         fsteps = max(3, min(args.steps, 5))
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
@@ -423,7 +520,13 @@ def main():
                          "bytes_per_frame": BYTES_PER_FRAME,
                          "note": "integer-issue bound, not HBM bound: see DESIGN.md"},
             "e2e": {"value": e2e_value, "unit": "frames/s",
-                    "h2d_bytes_per_step": ne * N_SAMPLES * 2, "d2h_bytes_per_step": ne * K * NCEP * 2},
+                    "h2d_bytes_per_step": ne * N_SAMPLES * 2, "d2h_bytes_per_step": ne * K * NCEP * 2,
+                    "ms_per_step": t_e2e * 1e3, "clips_per_gpu": ne, "steps": e_steps,
+                    "h2d_gbs_all_gpus": ne * N_SAMPLES * 2 * world / t_e2e / 1e9,
+                    "pipeline": "mfcc_b200_run_host: %s MiB chunks, %s in flight, 3 streams (H2D / kernel / D2H), "
+                                "1-D copies" % (args.e2e_chunk_mb or 32, args.e2e_slots or 4),
+                    "write_combined_source": bool(args.e2e_wc),
+                    "copy_ceiling": copy_ceiling},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         # instruction-issue view of the same kernel: warp-instructions per frame and DRAM bytes
@@ -442,6 +545,10 @@ def main():
                                          "peak_source": "profiles/micro/pipe_bench.cu IMAD+SHF 1:1 on this GPU model"}
         except Exception:
             pass
+        if e2e_sweep:
+            line["e2e"]["sweep"] = e2e_sweep
+        if c4:
+            line["c4"] = c4
         if extras:
             if "achieved_gbs" in extras.get("fp32", {}):
                 extras["fp32"]["hbm_frac"] = extras["fp32"]["achieved_gbs"] / peak
@@ -452,11 +559,15 @@ def main():
                 from oracle import ref_c as RC
                 thr = RC.max_threads()
                 ncl = min(256, 16 * thr)        # ~20 core-seconds of CPU work
-                v, fr, dt = cpu_oracle_rate(ncl, thr)
+                v, fr, dt = cpu_oracle_rate(ncl, thr, repeats=2)
                 v1, fr1, dt1 = cpu_oracle_rate(16, 1)       # also a single-thread figure
+                vc, frc, dtc = cpu_oracle_rate(min(ncl, 4 * thr), thr, fast=False)
                 line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": thr, "kind": "port",
                                         "sample": "%d clips x 60 s (%d frames), %.1f s" % (ncl, fr, dt),
-                                        "single_thread": {"value": v1, "sample": "16 clips x 60 s, %.1f s" % dt1}}
+                                        "build_flags": "gcc " + RC.FAST_FLAGS, "source": "oracle/mfcc_ref_fast.c",
+                                        "single_thread": {"value": v1, "sample": "16 clips x 60 s, %.1f s" % dt1},
+                                        "checker_build": {"value": vc, "build_flags": "gcc -O2 -fopenmp",
+                                                          "source": "oracle/mfcc_ref.c", "cores": thr}}
             except Exception as e:      # noqa: BLE001
                 line["cpu_baseline"] = {"value": None, "unit": "frames/s", "cores": 0, "kind": "port",
                                         "sample": "failed: %s: %s" % (type(e).__name__, e)}

@@ -126,6 +126,30 @@ int  mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, i
                         int32_t n_clips, int64_t n_frames, void *h_out, int64_t out_clip_stride);
 
 /*
+ * Staging pipeline of mfcc_b200_run_host: chunks of `chunk_bytes` of samples (default 32 MiB),
+ * `slots` of them in flight (2..8, default 4) on three streams chained by events: host->device
+ * copy, kernel, device->host copy.  0 keeps the current value.  Rows that are packed on the host
+ * at the device pitch (clip_stride == n_samples rounded up to 8, out_clip_stride ==
+ * n_frames*nceptrums) move with one plain copy per chunk and direction, anything else with one
+ * pitched copy.  Whatever happens inside the call, no copy or kernel of it is in flight when it
+ * returns (an error is returned after all three streams have drained).
+ */
+int  mfcc_b200_host_config(void *handle, int64_t chunk_bytes, int32_t slots);
+
+/*
+ * Page-locked host memory for the buffers of mfcc_b200_run_host / _step_host (what a host tool
+ * in the place of software/main.c:115-127, which mallocs its sample buffer, would use).
+ * write_combined != 0: uncached on the CPU side, for buffers the CPU only writes.
+ */
+int  mfcc_b200_host_alloc(void **p, int64_t bytes, int32_t write_combined);
+void mfcc_b200_host_free(void *p);
+
+/* Test hook: make chunk number `chunk` (0-based) of the next mfcc_b200_run_host calls fail after
+ * its host->device copy has been queued (-1 = off).  tests/test_gpu_parity.py uses it to check
+ * that an error inside the pipeline still leaves the caller's buffers quiescent. */
+int  mfcc_b200_debug_fail_chunk(void *handle, int32_t chunk);
+
+/*
  * One stage on its own (device buffers), the analogue of instantiating a single
  * stage module (constructors listed in the enum above).  n is the number of input
  * samples for PREEMPH and FRAME and the number of frames K otherwise; for FRAME

@@ -70,6 +70,14 @@ def lib():
     L.mfcc_b200_run.argtypes = [vp, vp, i64, i64, i32, i64, vp, i64, C.POINTER(Taps), vp]
     L.mfcc_b200_run_host.restype = C.c_int
     L.mfcc_b200_run_host.argtypes = [vp, vp, i64, i64, i32, i64, vp, i64]
+    L.mfcc_b200_host_config.restype = C.c_int
+    L.mfcc_b200_host_config.argtypes = [vp, i64, i32]
+    L.mfcc_b200_debug_fail_chunk.restype = C.c_int
+    L.mfcc_b200_debug_fail_chunk.argtypes = [vp, i32]
+    L.mfcc_b200_host_alloc.restype = C.c_int
+    L.mfcc_b200_host_alloc.argtypes = [C.POINTER(vp), i64, i32]
+    L.mfcc_b200_host_free.restype = None
+    L.mfcc_b200_host_free.argtypes = [vp]
     L.mfcc_b200_stage.restype = C.c_int
     L.mfcc_b200_stage.argtypes = [vp, i32, vp, vp, i64, i64, i32, vp]
     L.mfcc_b200_state_bytes.restype = C.c_int
@@ -123,6 +131,7 @@ def lib():
 
 
 EXPORTS = ["mfcc_b200_create", "mfcc_b200_destroy", "mfcc_b200_run", "mfcc_b200_run_host",
+           "mfcc_b200_host_config", "mfcc_b200_host_alloc", "mfcc_b200_host_free", "mfcc_b200_debug_fail_chunk",
            "mfcc_b200_stage", "mfcc_b200_frame", "mfcc_b200_window", "mfcc_b200_fft_stream",
            "mfcc_b200_dct_stream", "mfcc_b200_power", "mfcc_b200_log2fix", "mfcc_b200_filterbank", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_step_host", "mfcc_b200_lifter",
            "mfcc_b200_standardize", "mfcc_b200_to_int16", "mfcc_b200_uart_frame", "mfcc_b200_vad_step",

@@ -15,6 +15,7 @@
 #include <cmath>
 #include <cuda_runtime.h>
 #include <atomic>
+#include <initializer_list>
 #include <string>
 #include <vector>
 
@@ -102,6 +103,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "MBAR_DONE:\n"
         "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// Orders this thread's earlier generic-proxy accesses to shared memory (made visible to it by the
+// preceding __syncthreads) before later async-proxy writes (the bulk copy that refills the buffer).
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 // TMA 1-D bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -233,6 +237,7 @@ __device__ __forceinline__ void issue_tile(const RunParams &p, const TileIter &i
     const Tile g = tile_geo<SH::FT>(p, it.ci, it.ti);
     const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
     if (bytes) {
+        fence_proxy_async();
         mbar_arrive_expect_tx(&sm->mbar, bytes);
         tma_load_1d(sm->raw + g.lo, g.clip + g.a0 + g.lo, bytes, &sm->mbar);
     } else {
@@ -327,6 +332,7 @@ __device__ __forceinline__ void issue_tile_f(const RunParams &p, const TileIter 
     const Tile g = tile_geo<FT_F>(p, it.ci, it.ti);
     const uint32_t bytes = (uint32_t)(g.hi - g.lo) * 2u;
     if (bytes) {
+        fence_proxy_async();
         mbar_arrive_expect_tx(&sm->mbar[buf], bytes);
         tma_load_1d(sm->raw[buf] + g.lo, g.clip + g.a0 + g.lo, bytes, &sm->mbar[buf]);
     } else {
@@ -697,18 +703,33 @@ int fail(int code, const std::string &msg) { g_err = msg; return code; }
             return fail(MFCC_B200_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));  \
     } while (0)
 
+// Staging pipeline of mfcc_b200_run_host: chunks of clips travel host -> device on one stream,
+// are computed on a second and travel back on a third, chained by events, with up to
+// HOST_SLOTS chunks in flight so that both copy engines and the SMs stay busy at once.
+constexpr int HOST_SLOTS_MAX = 8;
+struct HostPipe {
+    cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
+    int16_t *d_in[HOST_SLOTS_MAX] = {nullptr};
+    void *d_out[HOST_SLOTS_MAX] = {nullptr};
+    cudaEvent_t ev_in[HOST_SLOTS_MAX] = {nullptr};    // chunk has arrived in d_in[slot]
+    cudaEvent_t ev_run[HOST_SLOTS_MAX] = {nullptr};   // kernel done: d_in[slot] free, d_out[slot] full
+    cudaEvent_t ev_out[HOST_SLOTS_MAX] = {nullptr};   // d_out[slot] has left for the host
+    size_t in_cap = 0, out_cap = 0;
+    int slots_alloc = 0;
+    long long chunk_bytes = 32LL << 20;               // samples per chunk (mfcc_b200_host_config)
+    int slots = 4;
+    int fail_at_chunk = -1;                           // test hook: mfcc_b200_debug_fail_chunk
+};
+
 struct Handle {
     mfcc_b200_cfg cfg;
     DevTables *d_tab = nullptr;
     mfccf::DevTablesF *d_ftab = nullptr;
     int device = 0;
     int sm_count = 0;
-    // staging for mfcc_b200_run_host
-    cudaStream_t st[2] = {nullptr, nullptr};
-    int16_t *d_in[2] = {nullptr, nullptr};
-    void *d_out[2] = {nullptr, nullptr};
-    size_t in_cap = 0, out_cap = 0;
+    HostPipe hp;                                      // staging for mfcc_b200_run_host
     // state and staging of mfcc_b200_step_host
+    cudaStream_t s_step = nullptr;
     void *s_state = nullptr, *s_out = nullptr;
     int16_t *s_hop = nullptr;
     int s_streams = 0;
@@ -910,6 +931,45 @@ int set_smem(K kernel, size_t bytes) {
     return MFCC_B200_OK;
 }
 
+// (Re)allocate the staging pipeline; on failure everything is released again and the pipe is
+// left empty (the next call starts from scratch).
+void host_pipe_free(HostPipe &hp, bool streams) {
+    for (int i = 0; i < HOST_SLOTS_MAX; ++i) {
+        if (hp.d_in[i]) cudaFree(hp.d_in[i]);
+        if (hp.d_out[i]) cudaFree(hp.d_out[i]);
+        hp.d_in[i] = nullptr; hp.d_out[i] = nullptr;
+        if (streams) {
+            for (cudaEvent_t *ev : {&hp.ev_in[i], &hp.ev_run[i], &hp.ev_out[i]})
+                if (*ev) { cudaEventDestroy(*ev); *ev = nullptr; }
+        }
+    }
+    hp.in_cap = hp.out_cap = 0;
+    hp.slots_alloc = 0;
+    if (streams) {
+        for (cudaStream_t *st : {&hp.s_in, &hp.s_run, &hp.s_out})
+            if (*st) { cudaStreamDestroy(*st); *st = nullptr; }
+    }
+}
+
+int host_pipe_alloc(HostPipe &hp, size_t in_need, size_t out_need, int slots) {
+    host_pipe_free(hp, false);
+    cudaError_t e = cudaSuccess;
+    for (cudaStream_t *st : {&hp.s_in, &hp.s_run, &hp.s_out})
+        if (e == cudaSuccess && !*st) e = cudaStreamCreateWithFlags(st, cudaStreamNonBlocking);
+    for (int i = 0; i < slots && e == cudaSuccess; ++i) {
+        for (cudaEvent_t *ev : {&hp.ev_in[i], &hp.ev_run[i], &hp.ev_out[i]})
+            if (e == cudaSuccess && !*ev) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaMalloc(&hp.d_in[i], in_need);
+        if (e == cudaSuccess) e = cudaMalloc(&hp.d_out[i], out_need);
+    }
+    if (e != cudaSuccess) {
+        host_pipe_free(hp, false);
+        return fail(MFCC_B200_ECUDA, std::string("mfcc_b200_run_host: staging buffers: ") + cudaGetErrorString(e));
+    }
+    hp.in_cap = in_need; hp.out_cap = out_need; hp.slots_alloc = slots;
+    return MFCC_B200_OK;
+}
+
 int check_handle(void *h) {
     if (!h) return fail(MFCC_B200_EINVAL, "null handle");
     return MFCC_B200_OK;
@@ -1012,11 +1072,8 @@ void mfcc_b200_destroy(void *handle)
 {
     Handle *h = static_cast<Handle *>(handle);
     if (!h) return;
-    for (int i = 0; i < 2; ++i) {
-        if (h->st[i]) cudaStreamDestroy(h->st[i]);
-        if (h->d_in[i]) cudaFree(h->d_in[i]);
-        if (h->d_out[i]) cudaFree(h->d_out[i]);
-    }
+    host_pipe_free(h->hp, true);
+    if (h->s_step) cudaStreamDestroy(h->s_step);
     if (h->s_state) cudaFree(h->s_state);
     if (h->s_hop) cudaFree(h->s_hop);
     if (h->s_out) cudaFree(h->s_out);
@@ -1079,11 +1136,43 @@ int mfcc_b200_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t
     return MFCC_B200_OK;
 }
 
+int mfcc_b200_host_config(void *handle, int64_t chunk_bytes, int32_t slots)
+{
+    if (int rc = check_handle(handle)) return rc;
+    Handle *h = static_cast<Handle *>(handle);
+    if (chunk_bytes < 0 || slots < 0 || slots > HOST_SLOTS_MAX || slots == 1)
+        return fail(MFCC_B200_EINVAL, "chunk_bytes >= 0 and slots in 2..8 (0 keeps the current value)");
+    if (chunk_bytes) h->hp.chunk_bytes = chunk_bytes;
+    if (slots) h->hp.slots = slots;
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_debug_fail_chunk(void *handle, int32_t chunk)
+{
+    if (int rc = check_handle(handle)) return rc;
+    static_cast<Handle *>(handle)->hp.fail_at_chunk = chunk;
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_host_alloc(void **p, int64_t bytes, int32_t write_combined)
+{
+    if (!p || bytes <= 0) return fail(MFCC_B200_EINVAL, "bad argument");
+    *p = nullptr;
+    CUDA_TRY(cudaHostAlloc(p, (size_t)bytes, write_combined ? cudaHostAllocWriteCombined : cudaHostAllocDefault));
+    return MFCC_B200_OK;
+}
+
+void mfcc_b200_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
 int mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, int64_t n_samples, int32_t n_clips,
                        int64_t n_frames, void *h_out, int64_t out_clip_stride)
 {
     if (int rc = check_handle(handle)) return rc;
     Handle *h = static_cast<Handle *>(handle);
+    HostPipe &hp = h->hp;
     if (n_clips < 0 || n_frames < 0 || n_samples < 0) return fail(MFCC_B200_EINVAL, "negative size");
     if (n_clips == 0 || n_frames == 0) return MFCC_B200_OK;
     if (!h_x || !h_out) return fail(MFCC_B200_EINVAL, "null buffer");
@@ -1092,45 +1181,70 @@ int mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, in
     const int nc = h->cfg.nceptrums;
     const long long in_row = n_samples ? ((n_samples + 7) & ~7LL) : 8;   // device row pitch: 16-byte multiple (TMA)
     const long long out_row = n_frames * nc;
-    // chunks of clips sized for ~32 MiB of samples; two streams alternate so that the
-    // copy-in of one chunk, the kernel of another and the copy-out overlap on PCIe
-    long long per = (32LL << 20) / (in_row * 2);
+    long long per = hp.chunk_bytes / (in_row * 2);                       // clips per chunk
     if (per < 1) per = 1;
     if (per > n_clips) per = n_clips;
+    const long long n_chunks = (n_clips + per - 1) / per;
+    const int slots = (int)(n_chunks < hp.slots ? n_chunks : hp.slots);
     const size_t esz = h->cfg.mode == MFCC_B200_MODE_FP32 ? sizeof(float) : sizeof(int16_t);   // output element
     const size_t in_need = (size_t)per * in_row * 2, out_need = (size_t)per * out_row * esz;
-    if (in_need > h->in_cap || out_need > h->out_cap) {
-        for (int i = 0; i < 2; ++i) {
-            if (h->d_in[i]) cudaFree(h->d_in[i]);
-            if (h->d_out[i]) cudaFree(h->d_out[i]);
-            h->d_in[i] = nullptr; h->d_out[i] = nullptr;
-        }
-        h->in_cap = h->out_cap = 0;
-        for (int i = 0; i < 2; ++i) {
-            if (!h->st[i]) CUDA_TRY(cudaStreamCreateWithFlags(&h->st[i], cudaStreamNonBlocking));
-            CUDA_TRY(cudaMalloc(&h->d_in[i], in_need));
-            CUDA_TRY(cudaMalloc(&h->d_out[i], out_need));
-        }
-        h->in_cap = in_need; h->out_cap = out_need;
-    }
-    unsigned char *out8 = static_cast<unsigned char *>(h_out);
-    int slot = 0;
-    for (long long done = 0; done < n_clips; slot ^= 1) {
-        const long long n = (n_clips - done) < per ? (n_clips - done) : per;
-        cudaStream_t s = h->st[slot];
-        // straight from / to the caller's buffers: full PCIe rate when they are pinned
-        if (n_samples)
-            CUDA_TRY(cudaMemcpy2DAsync(h->d_in[slot], (size_t)in_row * 2, h_x + done * clip_stride, (size_t)clip_stride * 2,
-                                       (size_t)n_samples * 2, (size_t)n, cudaMemcpyHostToDevice, s));
-        if (int rc = mfcc_b200_run(h, h->d_in[slot], in_row, n_samples, (int32_t)n, n_frames, h->d_out[slot], out_row,
-                                   nullptr, s))
+    if (in_need > hp.in_cap || out_need > hp.out_cap || slots > hp.slots_alloc)
+        if (int rc = host_pipe_alloc(hp, in_need > hp.in_cap ? in_need : hp.in_cap,
+                                     out_need > hp.out_cap ? out_need : hp.out_cap, slots > hp.slots_alloc ? slots : hp.slots_alloc))
             return rc;
-        CUDA_TRY(cudaMemcpy2DAsync(out8 + (size_t)done * out_clip_stride * esz, (size_t)out_clip_stride * esz, h->d_out[slot],
-                                   (size_t)out_row * esz, (size_t)out_row * esz, (size_t)n, cudaMemcpyDeviceToHost, s));
+    // rows packed at the device pitch on the host too: one plain copy per chunk, else a pitched one
+    const bool in_1d = n_clips == 1 || clip_stride == in_row;
+    const bool out_1d = n_clips == 1 || out_clip_stride == out_row;
+    unsigned char *out8 = static_cast<unsigned char *>(h_out);
+    cudaError_t e = cudaSuccess;
+    const char *what = "";
+    int rc = MFCC_B200_OK;
+    long long done = 0;
+    for (long long c = 0; c < n_chunks && e == cudaSuccess && rc == MFCC_B200_OK; ++c) {
+        const int slot = (int)(c % slots);
+        const long long n = (n_clips - done) < per ? (n_clips - done) : per;
+        // host -> device, once the kernel that last read d_in[slot] is done
+        if (c >= slots) e = cudaStreamWaitEvent(hp.s_in, hp.ev_run[slot], 0), what = "cudaStreamWaitEvent";
+        if (e == cudaSuccess && n_samples) {
+            what = "host->device copy";
+            if (in_1d)
+                e = cudaMemcpyAsync(hp.d_in[slot], h_x + done * clip_stride, (size_t)((n - 1) * in_row + n_samples) * 2,
+                                    cudaMemcpyHostToDevice, hp.s_in);
+            else
+                e = cudaMemcpy2DAsync(hp.d_in[slot], (size_t)in_row * 2, h_x + done * clip_stride, (size_t)clip_stride * 2,
+                                      (size_t)n_samples * 2, (size_t)n, cudaMemcpyHostToDevice, hp.s_in);
+        }
+        if (e == cudaSuccess && hp.fail_at_chunk == (int)c) e = cudaErrorUnknown, what = "injected failure (mfcc_b200_debug_fail_chunk)";
+        if (e == cudaSuccess) e = cudaEventRecord(hp.ev_in[slot], hp.s_in), what = "cudaEventRecord";
+        // kernel, once the chunk is in and the copy that last read d_out[slot] is done
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(hp.s_run, hp.ev_in[slot], 0), what = "cudaStreamWaitEvent";
+        if (e == cudaSuccess && c >= slots) e = cudaStreamWaitEvent(hp.s_run, hp.ev_out[slot], 0);
+        if (e != cudaSuccess) break;
+        rc = mfcc_b200_run(h, hp.d_in[slot], in_row, n_samples, (int32_t)n, n_frames, hp.d_out[slot], out_row, nullptr, hp.s_run);
+        if (rc) break;
+        e = cudaEventRecord(hp.ev_run[slot], hp.s_run), what = "cudaEventRecord";
+        // device -> host
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(hp.s_out, hp.ev_run[slot], 0), what = "cudaStreamWaitEvent";
+        if (e == cudaSuccess) {
+            what = "device->host copy";
+            unsigned char *dst = out8 + (size_t)done * out_clip_stride * esz;
+            if (out_1d)
+                e = cudaMemcpyAsync(dst, hp.d_out[slot], (size_t)n * out_row * esz, cudaMemcpyDeviceToHost, hp.s_out);
+            else
+                e = cudaMemcpy2DAsync(dst, (size_t)out_clip_stride * esz, hp.d_out[slot], (size_t)out_row * esz,
+                                      (size_t)out_row * esz, (size_t)n, cudaMemcpyDeviceToHost, hp.s_out);
+        }
+        if (e == cudaSuccess) e = cudaEventRecord(hp.ev_out[slot], hp.s_out), what = "cudaEventRecord";
         done += n;
     }
-    CUDA_TRY(cudaStreamSynchronize(h->st[0]));
-    CUDA_TRY(cudaStreamSynchronize(h->st[1]));
+    // Whatever happened, nothing of this call may still be in flight when it returns: the caller
+    // owns h_x and h_out and may free them at once.
+    const cudaError_t e1 = cudaStreamSynchronize(hp.s_in), e2 = cudaStreamSynchronize(hp.s_run),
+                      e3 = cudaStreamSynchronize(hp.s_out);
+    if (rc) return rc;                                                   // message set by mfcc_b200_run
+    if (e != cudaSuccess) return fail(MFCC_B200_ECUDA, std::string("mfcc_b200_run_host: ") + what + ": " + cudaGetErrorString(e));
+    for (cudaError_t es : {e1, e2, e3})
+        if (es != cudaSuccess) return fail(MFCC_B200_ECUDA, std::string("mfcc_b200_run_host: cudaStreamSynchronize: ") + cudaGetErrorString(es));
     return MFCC_B200_OK;
 }
 
@@ -1235,7 +1349,7 @@ int mfcc_b200_step_host(void *handle, int32_t n_streams, const int16_t *h_hop, v
     if (n_streams < 1) return fail(MFCC_B200_EINVAL, "n_streams must be >= 1");
     const size_t esz = h->cfg.mode == MFCC_B200_MODE_FP32 ? sizeof(float) : sizeof(int16_t);
     const size_t state_bytes = (size_t)n_streams * STATE_N * sizeof(int16_t);
-    if (!h->st[0]) CUDA_TRY(cudaStreamCreateWithFlags(&h->st[0], cudaStreamNonBlocking));
+    if (!h->s_step) CUDA_TRY(cudaStreamCreateWithFlags(&h->s_step, cudaStreamNonBlocking));
     if (h->s_streams != n_streams) {
         if (h->s_state) cudaFree(h->s_state);
         if (h->s_hop) cudaFree(h->s_hop);
@@ -1247,16 +1361,16 @@ int mfcc_b200_step_host(void *handle, int32_t n_streams, const int16_t *h_hop, v
         h->s_streams = n_streams;
         reset = 1;
     }
-    if (reset) CUDA_TRY(cudaMemsetAsync(h->s_state, 0, state_bytes, h->st[0]));      // the reset of every stream
+    if (reset) CUDA_TRY(cudaMemsetAsync(h->s_state, 0, state_bytes, h->s_step));      // the reset of every stream
     if (!h_hop) {                                                                    // reset only
-        CUDA_TRY(cudaStreamSynchronize(h->st[0]));
+        CUDA_TRY(cudaStreamSynchronize(h->s_step));
         return MFCC_B200_OK;
     }
     if (!h_out) return fail(MFCC_B200_EINVAL, "null buffer");
-    CUDA_TRY(cudaMemcpyAsync(h->s_hop, h_hop, (size_t)n_streams * HOP * sizeof(int16_t), cudaMemcpyHostToDevice, h->st[0]));
-    if (int rc = mfcc_b200_step(h, h->s_state, h->s_hop, n_streams, h->s_out, h->st[0])) return rc;
-    CUDA_TRY(cudaMemcpyAsync(h_out, h->s_out, (size_t)n_streams * h->cfg.nceptrums * esz, cudaMemcpyDeviceToHost, h->st[0]));
-    CUDA_TRY(cudaStreamSynchronize(h->st[0]));
+    CUDA_TRY(cudaMemcpyAsync(h->s_hop, h_hop, (size_t)n_streams * HOP * sizeof(int16_t), cudaMemcpyHostToDevice, h->s_step));
+    if (int rc = mfcc_b200_step(h, h->s_state, h->s_hop, n_streams, h->s_out, h->s_step)) return rc;
+    CUDA_TRY(cudaMemcpyAsync(h_out, h->s_out, (size_t)n_streams * h->cfg.nceptrums * esz, cudaMemcpyDeviceToHost, h->s_step));
+    CUDA_TRY(cudaStreamSynchronize(h->s_step));
     return MFCC_B200_OK;
 }
 

@@ -27,6 +27,34 @@ def _stream_ptr(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+class _PinnedBlock:
+    """Owner of one mfcc_b200_host_alloc block (freed when the last tensor view dies)."""
+
+    def __init__(self, nbytes, write_combined):
+        p = C.c_void_p()
+        _lib.check(_lib.lib().mfcc_b200_host_alloc(C.byref(p), nbytes, 1 if write_combined else 0))
+        self.ptr, self.nbytes = p.value, nbytes
+
+    def __del__(self):
+        try:
+            _lib.lib().mfcc_b200_host_free(C.c_void_p(self.ptr))
+        except Exception:       # noqa: BLE001 - interpreter shutdown
+            pass
+
+
+def pinned_empty(shape, dtype=torch.int16, write_combined=False):
+    """A page-locked host tensor from the library's own allocator (mfcc_b200_host_alloc),
+    optionally write-combined (for sample buffers the CPU only fills).  Needs a CUDA device."""
+    n = 1
+    for d in shape:
+        n *= int(d)
+    nbytes = max(1, n) * torch.empty((), dtype=dtype).element_size()
+    blk = _PinnedBlock(nbytes, write_combined)
+    buf = (C.c_char * nbytes).from_address(blk.ptr)
+    buf._owner = blk                                 # keeps the block alive as long as the tensor's buffer
+    return torch.frombuffer(buf, dtype=dtype, count=n).reshape(tuple(shape))
+
+
 def _check_samples(x, device):
     if not isinstance(x, torch.Tensor):
         raise TypeError("samples must be a torch.Tensor")
@@ -196,6 +224,16 @@ class MFCC:
             t["frame"] = frames[0]
             return out[0], t
         return out[0] if single else out
+
+    def host_config(self, chunk_mb=None, slots=None):
+        """Staging pipeline of run_host (mfcc_b200_host_config): chunk size in MiB of
+        samples and the number of chunks in flight (2..8)."""
+        if self._composed:
+            return self
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().mfcc_b200_host_config(
+                self._h.ptr, 0 if chunk_mb is None else int(chunk_mb * (1 << 20)), 0 if slots is None else int(slots)))
+        return self
 
     def run_host(self, samples, n_frames=None, out=None):
         """Host buffers in, host buffers out (pinned buffers give full PCIe rate):

@@ -39,7 +39,50 @@ def build(force: bool = False) -> str:
     return _SO
 
 
+FAST_FLAGS = "-O3 -march=native -fopenmp"
+
+
+def _cpu_tag() -> str:
+    """Hash of this machine's CPU feature flags: a -march=native binary is only valid here."""
+    import hashlib
+    flags = ""
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("flags"):
+                flags = line
+                break
+    except OSError:
+        pass
+    return hashlib.sha1(flags.encode()).hexdigest()[:10]
+
+
+def build_fast(force: bool = False) -> str:
+    """Compile the timed CPU baseline (oracle/mfcc_ref_fast.c, gcc -O3 -march=native -fopenmp)
+    on THIS machine; the file name carries a hash of the CPU flags so that a binary built
+    elsewhere is never loaded."""
+    so = os.path.join(_HERE, "libmfcc_ref_fast.%s.so" % _cpu_tag())
+    src = os.path.join(_HERE, "mfcc_ref_fast.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "fast", "FAST_SO=" + os.path.basename(so)])
+    return so
+
+
 _lib = None
+_fast = None
+
+
+def _bind_run(L):
+    L.mfcc_ref_run.restype = C.c_int
+    L.mfcc_ref_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32,
+                               C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32]
+    return L
+
+
+def fast_lib():
+    global _fast
+    if _fast is None:
+        _fast = _bind_run(C.CDLL(build_fast()))
+    return _fast
 
 
 def lib():
@@ -97,9 +140,12 @@ def max_threads() -> int:
         return max(1, os.cpu_count() or int(lib().mfcc_ref_max_threads()))
 
 
-def run(cfg: RefConfig, x: np.ndarray, n_frames=None, taps=False, threads=1):
+def run(cfg: RefConfig, x: np.ndarray, n_frames=None, taps=False, threads=1, fast=False):
     """x: int16 [N] or [B, N].  Returns int16 [K, nceptrums] / [B, K, nceptrums]
-    (and a dict of per-stage arrays of clip 0 when taps=True)."""
+    (and a dict of per-stage arrays of clip 0 when taps=True).  fast=True runs the tuned
+    build (mfcc_ref_fast.c, the timed CPU baseline) instead of the checker."""
+    if fast and taps:
+        raise ValueError("the tuned build has no taps")
     x = np.ascontiguousarray(x, dtype=np.int16)
     single = x.ndim == 1
     x2 = x[None, :] if single else x
@@ -114,7 +160,7 @@ def run(cfg: RefConfig, x: np.ndarray, n_frames=None, taps=False, threads=1):
                  power=np.zeros((K, nb), np.uint32), mel=np.zeros((K, nf), np.uint16),
                  log2=np.zeros((K, nf), np.uint16), dct=np.zeros((K, nf), np.int16))
         tp = _Taps(*[t[n].ctypes.data for n in ("window", "fft", "power", "mel", "log2", "dct")])
-    rc = lib().mfcc_ref_run(C.byref(cfg.c), x2.ctypes.data, N, N, B, K, out.ctypes.data,
+    rc = (fast_lib() if fast else lib()).mfcc_ref_run(C.byref(cfg.c), x2.ctypes.data, N, N, B, K, out.ctypes.data,
                             K * cfg.nceptrums, C.byref(tp) if tp is not None else None, threads)
     if rc != 0:
         raise RuntimeError("mfcc_ref_run failed: %d" % rc)

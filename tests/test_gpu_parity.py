@@ -146,6 +146,71 @@ def test_run_host_equals_device_path(ops, RC):
     assert np.array_equal(m.run_host(torch.from_numpy(x)).numpy(), want)     # pageable too
 
 
+def test_run_host_pipeline_shapes(RC):
+    """mfcc_b200_run_host: chunks smaller than the batch (every staging slot reused several
+    times), 2..8 chunks in flight, rows packed (one plain copy per chunk) and pitched (2-D
+    copies), sample counts that are not multiples of 8, library-allocated pinned buffers."""
+    import ctypes as C
+    import mfcc_b200
+    from mfcc_b200 import _lib
+    from mfcc_b200.mfcc import pinned_empty
+    m = mfcc_b200.MFCC(nfilters=32, nceptrums=32)
+    cfg = RC.RefConfig(nfilters=32, nceptrums=32)
+    rng = np.random.default_rng(12)
+    for n, B in ((40000, 61), (39997, 23)):
+        x = rng.integers(-32768, 32768, (B, n)).astype(np.int16)
+        want = RC.run(cfg, x, threads=4)
+        K = want.shape[1]
+        xh = pinned_empty((B, n), torch.int16, write_combined=(n % 8 == 0))
+        xh.copy_(torch.from_numpy(x))
+        oh = pinned_empty((B, K, 32), torch.int16)
+        for mb, slots in ((0.25, 2), (0.25, 3), (0.5, 8), (32, 4)):
+            m.host_config(mb, slots)
+            oh.zero_()
+            assert np.array_equal(m.run_host(xh, out=oh).numpy(), want), (n, mb, slots)
+        # pitched rows on both sides, straight through the C ABI
+        pitch, opitch = n + 24, K * 32 + 40
+        xp = np.zeros((B, pitch), np.int16)
+        xp[:, :n] = x
+        op_ = np.full((B, opitch), -1, np.int16)
+        m.host_config(0.25, 3)
+        _lib.check(_lib.lib().mfcc_b200_run_host(m._h.ptr, C.c_void_p(xp.ctypes.data), pitch, n, B, K,
+                                                 C.c_void_p(op_.ctypes.data), opitch))
+        assert np.array_equal(op_[:, :K * 32].reshape(B, K, 32), want) and (op_[:, K * 32:] == -1).all()
+    with pytest.raises(_lib.MfccError):
+        m.host_config(1, 1)
+    with pytest.raises(_lib.MfccError):
+        m.host_config(1, 9)
+
+
+def test_run_host_error_leaves_nothing_in_flight(RC):
+    """A failure in the middle of the staging pipeline (injected after chunk 2's host->device copy
+    has been queued) is reported only after all three streams have drained: the caller may free
+    its buffers at once, and the handle keeps working."""
+    import mfcc_b200
+    from mfcc_b200 import _lib
+    m = mfcc_b200.MFCC(nfilters=32, nceptrums=16)
+    cfg = RC.RefConfig(nfilters=32, nceptrums=16)
+    rng = np.random.default_rng(13)
+    x = rng.integers(-32768, 32768, (40, 64000)).astype(np.int16)
+    want = RC.run(cfg, x, threads=4)
+    m.host_config(0.5, 3)                                   # 4 clips per chunk, 10 chunks
+    xh = torch.from_numpy(x).pin_memory()
+    oh = torch.full(want.shape, -7, dtype=torch.int16).pin_memory()
+    _lib.check(_lib.lib().mfcc_b200_debug_fail_chunk(m._h.ptr, 2))
+    with pytest.raises(_lib.MfccError, match="injected failure"):
+        m.run_host(xh, out=oh)
+    assert torch.cuda.current_stream().query()
+    got = oh.numpy().copy()
+    # chunks 0 and 1 are complete, nothing of chunk 2.. was written, and nothing arrives later
+    assert np.array_equal(got[:8], want[:8]) and (got[8:] == -7).all()
+    del xh
+    torch.cuda.synchronize()
+    assert np.array_equal(oh.numpy(), got)
+    _lib.check(_lib.lib().mfcc_b200_debug_fail_chunk(m._h.ptr, -1))
+    assert np.array_equal(m.run_host(torch.from_numpy(x)).numpy(), want)
+
+
 @pytest.mark.parametrize("frames", [100, 200])
 def test_many_short_clips(ops, RC, frames):
     """2000 short clips in one launch: 200 frames each take the 72-frame tiles (three per clip,

@@ -181,6 +181,25 @@ def test_chain_edge_inputs(nf, nc):
             assert a.shape == b.shape and np.array_equal(a, b), (name, nfr)
 
 
+@pytest.mark.parametrize("nf,nc", [(32, 32), (32, 13), (16, 16)])
+def test_timed_baseline_equals_checker(nf, nc, wav):
+    """oracle/mfcc_ref_fast.c (gcc -O3 -march=native -fopenmp, the build bench.py times as
+    cpu_baseline / --impl reference) must be the checker's arithmetic bit for bit."""
+    cfg = RC.RefConfig(nfilters=nf, nceptrums=nc)
+    rng = np.random.default_rng(11)
+    n = 20000
+    x = np.stack([
+        rng.integers(-32768, 32768, n), (rng.standard_normal(n) * 2000).clip(-32768, 32767),
+        np.tile([-32768, 32767], n // 2), np.tile([32767, 32767, -32768, -32768], n // 4),
+        np.full(n, 32767), np.full(n, -32768), np.zeros(n), (np.arange(n) == 700) * 32767,
+        wav[:n], np.ones(n)]).astype(np.int16)
+    assert np.array_equal(RC.run(cfg, x, fast=True, threads=2), RC.run(cfg, x))
+    # ragged: frames past the end of the clip read zeros; a single row; more threads than clips
+    assert np.array_equal(RC.run(cfg, x[:, :700], n_frames=9, fast=True), RC.run(cfg, x[:, :700], n_frames=9))
+    assert np.array_equal(RC.run(cfg, x[0], fast=True, threads=4), RC.run(cfg, x[0]))
+    assert "-march=native" in RC.FAST_FLAGS and "-O3" in RC.FAST_FLAGS
+
+
 def test_float_sanity(wav):
     """The integer chain tracks a float pipeline of the same structure (loose bound:
     guards against gross restatement errors, e.g. a wrong shift)."""
