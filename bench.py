@@ -390,7 +390,7 @@ def main():
             op.host_config(mb, sl)
             ts = timed_host(lambda: op.run_host(xh, out=oh), max(2, e_steps // 2))
             e2e_sweep.append({"chunk_mb": mb, "slots": sl, "value": ne * K * world / ts})
-        op.host_config(args.e2e_chunk_mb or 32, args.e2e_slots or 4)
+        op.host_config(args.e2e_chunk_mb or 16, args.e2e_slots or 4)
     del xd, od, xh, oh
 
     # ---- C4 (BASELINE.json configs[3]): 10^6 audio-seconds = 16 667 clips of 60 s, rank r of G
@@ -524,7 +524,7 @@ def main():
                     "ms_per_step": t_e2e * 1e3, "clips_per_gpu": ne, "steps": e_steps,
                     "h2d_gbs_all_gpus": ne * N_SAMPLES * 2 * world / t_e2e / 1e9,
                     "pipeline": "mfcc_b200_run_host: %s MiB chunks, %s in flight, 3 streams (H2D / kernel / D2H), "
-                                "1-D copies" % (args.e2e_chunk_mb or 32, args.e2e_slots or 4),
+                                "1-D copies" % (args.e2e_chunk_mb or 16, args.e2e_slots or 4),
                     "write_combined_source": bool(args.e2e_wc),
                     "copy_ceiling": copy_ceiling},
             "gpu_launches": int(launches), "clocks": clocks,

@@ -126,7 +126,7 @@ int  mfcc_b200_run_host(void *handle, const int16_t *h_x, int64_t clip_stride, i
                         int32_t n_clips, int64_t n_frames, void *h_out, int64_t out_clip_stride);
 
 /*
- * Staging pipeline of mfcc_b200_run_host: chunks of `chunk_bytes` of samples (default 32 MiB),
+ * Staging pipeline of mfcc_b200_run_host: chunks of `chunk_bytes` of samples (default 16 MiB),
  * `slots` of them in flight (2..8, default 4) on three streams chained by events: host->device
  * copy, kernel, device->host copy.  0 keeps the current value.  Rows that are packed on the host
  * at the device pitch (clip_stride == n_samples rounded up to 8, out_clip_stride ==

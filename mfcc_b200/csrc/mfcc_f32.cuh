@@ -4,10 +4,12 @@
 // prototype notebook/MFCC-INT.ipynb cells 2-10 (pre-emphasis 0.96875, periodic Hamming,
 // fft/512 with 257 bins, |X|^2, dense triangular mel filters, log2, orthonormal DCT-II).
 //
-// One warp = one frame.  The 512 real samples are packed into 256 complex values and
-// transformed as 8 x 8 x 4: two radix-8 passes inside the lanes with one transpose
-// through shared memory, a radix-4 pass across groups of four lanes by shuffles, then
-// the split of the packed spectrum into bins 0..256 fused with the power spectrum.
+// Half a warp = one frame through the spectrum, a whole warp = one frame through mel/log/DCT;
+// a warp carries two frames at a time.  The 512 real samples are packed into 256 complex
+// values and transformed as 16 x 16: one 16-point DFT inside each of 16 lanes, twiddles, ONE
+// transpose through shared memory, a second 16-point DFT inside the lanes; the split of the
+// packed spectrum into bins 0..256 (fused with the power spectrum) takes its conjugate
+// partners from the mirror lane by shuffles.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -17,17 +19,21 @@ namespace mfccf {
 constexpr int NFFT = 512;
 constexpr int HOP = 170;
 constexpr int NBINS1 = 257;            // the notebook keeps bins 0..256 (cell 5)
-constexpr int XWF = 1040;              // 32-bit words of the per-warp exchange buffer
-constexpr int T1_STRIDE = 36;          // float2 per row of the first transpose
-constexpr int PW_OFF = 576;            // power spectrum lives behind the transpose area
-constexpr int PW_WORDS = XWF - PW_OFF; // padded power-spectrum area: see DevTablesF::paddr
+constexpr int XWF = 592;               // 32-bit words of one frame's exchange buffer (= 16 mod 32: the buffers of the
+                                       // two half-warps lie 16 banks apart)
+constexpr int T_PITCH = 18;            // float2 per row of the transpose: 64-bit row stores and 128-bit column
+                                       // loads are both conflict free at this pitch
+constexpr int PW_OFF = 0;              // the power spectrum overwrites the transpose area (16 * T_PITCH * 2 = 576 words)
+constexpr int PW_WORDS = 464;          // padded power-spectrum area: see DevTablesF::paddr
+constexpr int LM_OFF = 480;            // log-mel row of the frame (NF words), behind the power area
+static_assert(16 * T_PITCH * 2 <= XWF && LM_OFF + 32 <= XWF && LM_OFF >= PW_WORDS, "exchange buffer layout");
 constexpr int MEL_J0 = 7;              // 32 filters: segments 1..16 have at most 7 bins (checked by create)
 constexpr unsigned FULL = 0xffffffffu;
 
 struct alignas(16) DevTablesF {
-    float  window[NFFT];               // hamming(512, periodic) / 32: see emph_win()
-    float2 twA[8 * 32];                // [k1][lane]  exp(-2 pi i lane k1 / 256)
-    float2 twB[8 * 4];                 // [p][c]      exp(-2 pi i c p / 32)
+    float  window[NFFT];               // hamming(512, periodic)
+    float2 tw16[16 * 16];              // [k2][n1]    exp(-2 pi i n1 k2 / 256)
+    uint32_t pst[8 * 16];              // [k1][l]     paddr[16 k1 + l] | paddr[256 - (16 k1 + l)] << 16
     float2 tw512[132];                 // exp(-2 pi i k / 512), k = 0..128
     float  dct[16 * 32];               // dct[n * 32 + k] = D[k][n], n < nfilters / 2 (the rest by symmetry)
     float2 melw[672];                  // [step][lane] (rise weight, fall weight) of the lane's segment
@@ -74,126 +80,144 @@ __device__ __forceinline__ void fft8(float2 (&v)[8])
 }
 __host__ __device__ constexpr int brev3(int v) { return ((v & 1) << 2) | (v & 2) | ((v & 4) >> 2); }
 
-// Pre-emphasis + window for the two samples of one 32-bit word (samples 2n, 2n+1).
-//   y = x - 0.96875 * xp = (32 x - 31 xp) / 32 is an exact integer / 32 (|.| < 2^21), so
-// it is formed in integer arithmetic and turned into a float by the 1.5 * 2^23 bias
-// trick (no I2F); the 1/32 is folded into the window table.
-__device__ __forceinline__ float2 emph_win(unsigned w, unsigned wprev, float w0, float w1)
+// 16-point forward DFT in registers (decimation in frequency: one radix-2 stage with the
+// W16 twiddles, then two 8-point DFTs); on return v[j] holds bin k16(j).
+__host__ __device__ constexpr int k16(int j) { return j < 8 ? 2 * brev3(j) : 2 * brev3(j - 8) + 1; }
+__host__ __device__ constexpr int j16(int k) { return (k & 1) ? 8 + brev3(k >> 1) : brev3(k >> 1); }   // inverse of k16
+__device__ __forceinline__ void fft16(float2 (&v)[16])
 {
-    const int x0 = (int)(short)(w & 0xffffu), x1 = (int)w >> 16, xp = (int)wprev >> 16;
-    constexpr int MAGIC = 0x4B400000;                      // 1.5 * 2^23 = 12582912.0f
-    const float f0 = __int_as_float(MAGIC + (32 * x0 - 31 * xp)) - 12582912.0f;
-    const float f1 = __int_as_float(MAGIC + (32 * x1 - 31 * x0)) - 12582912.0f;
-    return make_float2(f0 * w0, f1 * w1);
+    constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, R = 0.70710678118654752f;
+    float2 e[8], o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        e[i] = cadd(v[i], v[i + 8]);
+        const float2 b = csub(v[i], v[i + 8]);
+        if (i == 0) o[0] = b;
+        else if (i == 1) o[1] = make_float2(fmaf(b.y, S1, b.x * C1), fmaf(b.x, -S1, b.y * C1));       // * (C1, -S1)
+        else if (i == 2) o[2] = make_float2((b.x + b.y) * R, (b.y - b.x) * R);                        // * (R, -R)
+        else if (i == 3) o[3] = make_float2(fmaf(b.y, C1, b.x * S1), fmaf(b.x, -C1, b.y * S1));       // * (S1, -C1)
+        else if (i == 4) o[4] = mul_mj(b);
+        else if (i == 5) o[5] = make_float2(fmaf(b.y, C1, b.x * -S1), fmaf(b.x, -C1, b.y * -S1));     // * (-S1, -C1)
+        else if (i == 6) o[6] = make_float2((b.y - b.x) * R, -(b.x + b.y) * R);                       // * (-R, -R)
+        else o[7] = make_float2(fmaf(b.y, S1, b.x * -C1), fmaf(b.x, -S1, b.y * -C1));                 // * (-C1, -S1)
+    }
+    fft8(e);
+    fft8(o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { v[j] = e[j]; v[8 + j] = o[j]; }
 }
 
-// index of packed-spectrum bin k in the exchange buffer (4 float2 of padding per 64)
-__device__ __forceinline__ int zaddr(int k) { return k + ((k >> 6) << 2); }
+// Pre-emphasis + window for the two samples of one 32-bit word (samples 2n, 2n+1).
+// int16 -> float without I2F: with its sign bit flipped a sample is the unsigned number
+// x + 32768; dropped into the low mantissa bits of 1.5 * 2^23 it reads 12582912 + 32768 + x as a
+// float, exactly.  y = x - 0.96875 xp = (32 x - 31 xp) / 32 is exactly representable
+// (|32 x - 31 xp| < 2^22), so the single rounding of the FFMA returns it exactly.
+__device__ __forceinline__ float2 emph_win(unsigned w, unsigned wprev, float w0, float w1)
+{
+    constexpr float BIAS = 12582912.0f + 32768.0f;
+    const unsigned u = w ^ 0x80008000u, up = wprev ^ 0x80008000u;
+    const float x0 = __uint_as_float(__byte_perm(u, 0x4B400000u, 0x7610)) - BIAS;
+    const float x1 = __uint_as_float(__byte_perm(u, 0x4B400000u, 0x7632)) - BIAS;
+    const float xp = __uint_as_float(__byte_perm(up, 0x4B400000u, 0x7632)) - BIAS;
+    return make_float2(fmaf(xp, -0.96875f, x0) * w0, fmaf(x0, -0.96875f, x1) * w1);
+}
 
 // ---------------------------------------------------------------------------------
-// Power spectrum |X[b]|^2 / 512^2, b = 0..256, of NFR frames into pw[] (shared memory).
-//   raw[f]: frame f's int16 samples in shared memory (even halfword offset), raw[f][-1] is
-//           the sample before the frame (0 at the start of a stream)
-//   xb[f]:  frame f's exchange buffer (XWF words)
-// The kernel is bound by shared-memory bandwidth, and more than half of a frame's
-// wavefronts are loads of tables that do not depend on the frame (window, twiddles, mel
-// weights, DCT matrix, layout addresses).  With NFR = 2 a warp carries two frames through
-// every phase together and loads each table entry once for both.
-template <int NFR>
-__device__ __forceinline__ void power_warp_f32(const int16_t *const (&raw)[NFR], float *const (&xb)[NFR],
+// Power spectrum |X[b]|^2 / 512^2, b = 0..256, of TWO frames into shared memory: the lower
+// half-warp works on one frame, the upper on the other, with the same instruction stream.
+//   raw: this lane's frame: its int16 samples in shared memory (even halfword offset), raw[-1]
+//        is the sample before the frame (0 at the start of a stream)
+//   xb:  this lane's frame's exchange buffer (XWF words); the buffers of the two frames lie
+//        16 banks apart, and so do their samples when the frames are 16 apart
+// Index plan (tests/lane_model.py: f32_plan): z[n] = (y[2n], y[2n+1]) w, n = n1 + 16 n2;
+// bin k = 16 k1 + k2:  Z[k] = sum_n1 W16^(n1 k1) W256^(n1 k2) sum_n2 W16^(n2 k2) z[n1 + 16 n2].
+// Pass 1: lane n1 holds n2 = 0..15 in registers; pass 2: lane k2 holds n1 = 0..15 and ends with
+// Z[16 k1 + k2], k1 = 0..15.  The real-input split pairs bin k with bin 256 - k =
+// 16 (15 - k1) + (16 - k2): lane 16 - k2, so a lane takes the pairs of its k1 = 0..7 and
+// receives the upper eight registers of its mirror lane (lane 0 mirrors itself, one
+// register further round: 256 - 16 k1 = 16 (16 - k1)).
+// NP frames per half-warp go through every phase together, so that each table entry (window,
+// twiddles, layout addresses) is loaded once for all of them: a shared-memory wavefront delivers
+// 128 bytes to the lanes whether or not the two half-warps ask for the same addresses, so a
+// table costs per frame what it costs per lane.
+template <int NP>
+__device__ __forceinline__ void power_pair_f32(const int16_t *const (&raw)[NP], float *const (&xb)[NP],
                                                const DevTablesF *tab, int lane)
 {
+    const int l = lane & 15;
     const float2 *win2 = reinterpret_cast<const float2 *>(tab->window);
-    // ---- z[n] = (y[2n] w[2n], y[2n+1] w[2n+1]), n = lane + 32 a
-    float2 v[NFR][8];
+    float2 v[NP][16];
 #pragma unroll
-    for (int a = 0; a < 8; ++a) {
-        const int n = lane + 32 * a;
+    for (int a = 0; a < 16; ++a) {
+        const int n = l + 16 * a;
         const float2 ww = win2[n];
 #pragma unroll
-        for (int f = 0; f < NFR; ++f) {
+        for (int f = 0; f < NP; ++f) {
             const unsigned *r32 = reinterpret_cast<const unsigned *>(raw[f]);
             v[f][a] = emph_win(r32[n], r32[n - 1], ww.x, ww.y);
         }
     }
-    // ---- pass 1: DFT-8 over a, twiddle W256^(lane * k1), transpose
+    // ---- pass 1: DFT-16 over n2, twiddle W256^(n1 k2), transposed store T[k2][n1]
 #pragma unroll
-    for (int f = 0; f < NFR; ++f) fft8(v[f]);
+    for (int f = 0; f < NP; ++f) fft16(v[f]);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int k1 = brev3(j);
+    for (int j = 0; j < 16; ++j) {
+        const int k2 = k16(j);
         float2 w = make_float2(1.0f, 0.0f);
-        if (k1) w = tab->twA[k1 * 32 + lane];
+        if (k2) w = tab->tw16[k2 * 16 + l];
 #pragma unroll
-        for (int f = 0; f < NFR; ++f) {
+        for (int f = 0; f < NP; ++f) {
             float2 y = v[f][j];
-            if (k1) y = cmul(y, w);
-            reinterpret_cast<float2 *>(xb[f])[k1 * T1_STRIDE + lane] = y;
+            if (k2) y = cmul(y, w);
+            reinterpret_cast<float2 *>(xb[f])[k2 * T_PITCH + l] = y;
         }
     }
     __syncwarp();
-    // lane = (k1, c): the 8 values l = c + 4 b of row k1
-    const int k1 = lane >> 2, c = lane & 3;
+    // lane k2 = l: row l of T, two entries per 128-bit load
 #pragma unroll
-    for (int f = 0; f < NFR; ++f)
+    for (int f = 0; f < NP; ++f)
 #pragma unroll
-        for (int b = 0; b < 8; ++b) v[f][b] = reinterpret_cast<const float2 *>(xb[f])[k1 * T1_STRIDE + c + 4 * b];
-    __syncwarp();
-    // ---- pass 2: DFT-8 over b, twiddle W32^(c p) = W256^(8 c p)
-#pragma unroll
-    for (int f = 0; f < NFR; ++f) fft8(v[f]);
-    // ---- pass 3: DFT-4 over c across the four lanes of a group; lane c ends with
-    //      q = {0, 2, 1, 3}[c] of Z[k1 + 8 p + 64 q]
-    const float sg = (c & 2) ? -1.0f : 1.0f, sg1 = (c & 1) ? -1.0f : 1.0f;
-    const int q = ((c & 1) << 1) | (c >> 1);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int p = brev3(j);
-        float2 w = make_float2(1.0f, 0.0f);
-        if (p) w = tab->twB[p * 4 + c];
-#pragma unroll
-        for (int f = 0; f < NFR; ++f) {
-            float2 y = v[f][j];
-            if (p) y = cmul(y, w);
-            float2 o;
-            o.x = __shfl_xor_sync(FULL, y.x, 2);
-            o.y = __shfl_xor_sync(FULL, y.y, 2);
-            y = make_float2(fmaf(sg, y.x, o.x), fmaf(sg, y.y, o.y));     // c<2: mine+other, else other-mine
-            if (c == 3) y = mul_mj(y);
-            o.x = __shfl_xor_sync(FULL, y.x, 1);
-            o.y = __shfl_xor_sync(FULL, y.y, 1);
-            y = make_float2(fmaf(sg1, y.x, o.x), fmaf(sg1, y.y, o.y));
-            reinterpret_cast<float2 *>(xb[f])[zaddr(k1 + 8 * p + 64 * q)] = y;
+        for (int q = 0; q < 8; ++q) {
+            const float4 t = reinterpret_cast<const float4 *>(xb[f])[l * (T_PITCH / 2) + q];
+            v[f][2 * q] = make_float2(t.x, t.y);
+            v[f][2 * q + 1] = make_float2(t.z, t.w);
         }
-    }
     __syncwarp();
+    // ---- pass 2: DFT-16 over n1: v[j16(k1)] = Z[16 k1 + l]
+#pragma unroll
+    for (int f = 0; f < NP; ++f) fft16(v[f]);
     // ---- split: X[k] = F + W512^k G, X[256-k] = conj(F - W512^k G), with
     //      F = (Z[k] + conj Z[256-k]) / 2, G = (Z[k] - conj Z[256-k]) / 2j
+    // Z[256 - (16 k1 + l)] is register 15 - k1 of the mirror lane (lane 0: its own register 16 - k1)
     constexpr float SC = 1.0f / (512.0f * 512.0f);          // fft / 512 (cell 5), squared
+    const int src = (lane & 16) | ((16 - l) & 15);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int k = lane + 32 * i;
+    for (int k1 = 0; k1 < 8; ++k1) {
+        const int k = 16 * k1 + l;
         const float2 w = tab->tw512[k];
-        const int pa = tab->paddr[k], pb = tab->paddr[256 - k];          // k = 0 gives bin 256
+        const unsigned pa = tab->pst[k1 * 16 + l];                      // where bins k and 256 - k go
 #pragma unroll
-        for (int f = 0; f < NFR; ++f) {
-            const float2 *xc = reinterpret_cast<const float2 *>(xb[f]);
-            float *pw = xb[f] + PW_OFF;
-            const float2 A = xc[zaddr(k)];
-            const float2 B = xc[zaddr((256 - k) & 255)];
+        for (int f = 0; f < NP; ++f) {
+            float2 s = v[f][j16(15 - k1)];
+            if (l == 0) s = v[f][j16((16 - k1) & 15)];
+            float2 B;
+            B.x = __shfl_sync(FULL, s.x, src);
+            B.y = __shfl_sync(FULL, s.y, src);
+            const float2 A = v[f][j16(k1)];
             const float2 F = make_float2(0.5f * (A.x + B.x), 0.5f * (A.y - B.y));
             const float2 G = make_float2(0.5f * (A.y + B.y), -0.5f * (A.x - B.x));
             const float2 T = cmul(G, w);
             const float2 X0 = cadd(F, T), X1 = csub(F, T);
-            pw[pa] = (X0.x * X0.x + X0.y * X0.y) * SC;
-            pw[pb] = (X1.x * X1.x + X1.y * X1.y) * SC;
+            float *pw = xb[f] + PW_OFF;
+            pw[pa & 0xffffu] = (X0.x * X0.x + X0.y * X0.y) * SC;
+            pw[pa >> 16] = (X1.x * X1.x + X1.y * X1.y) * SC;
         }
     }
-    if (lane == 0) {                                         // bin 128: W512^128 = -j
+    if (l == 0) {                                            // bin 128: W512^128 = -j
         const int pa = tab->paddr[128];
 #pragma unroll
-        for (int f = 0; f < NFR; ++f) {
-            const float2 A = reinterpret_cast<const float2 *>(xb[f])[zaddr(128)];
+        for (int f = 0; f < NP; ++f) {
+            const float2 A = v[f][j16(8)];
             xb[f][PW_OFF + pa] = (A.x * A.x + A.y * A.y) * SC;
         }
     }
@@ -201,7 +225,7 @@ __device__ __forceinline__ void power_warp_f32(const int16_t *const (&raw)[NFR],
 }
 
 // mel -> log2 -> DCT-II of the power spectra in xb[f] + PW_OFF (padded layout); lane k gets
-// coefficient k of frame f in out[f]; xb[f][0..NF) is scratch.  The filters are triangles
+// coefficient k of frame f in out[f]; xb[f][LM_OFF..LM_OFF+NF) is scratch.  The filters are triangles
 // (cell 7): bin b of segment g (the bins
 // between two filter points) carries the rising weight of filter g and the falling
 // weight of filter g-1, so lane g-1 walks segment g once with two multiply-adds per
@@ -268,7 +292,7 @@ __device__ __forceinline__ void cepstrum_warp_f32(float *const (&xb)[NFR], const
     for (int f = 0; f < NFR; ++f) {
         float up = __shfl_up_sync(FULL, u[f], 1);
         if (li == 0) up = 0.0f;
-        xb[f][lane] = __log2f(fmaxf(up + v[f], tab->mel_floor));
+        xb[f][LM_OFF + lane] = __log2f(fmaxf(up + v[f], tab->mel_floor));
     }
     // orthonormal DCT-II with D[k][NF-1-n] = (-1)^k D[k][n]: NF/2 multiply-adds per lane
     __syncwarp();
@@ -280,8 +304,8 @@ __device__ __forceinline__ void cepstrum_warp_f32(float *const (&xb)[NFR], const
         float4 a[NFR], b[NFR];
 #pragma unroll
         for (int f = 0; f < NFR; ++f) {
-            a[f] = reinterpret_cast<const float4 *>(xb[f])[q];                       // L[4q .. 4q+3]
-            b[f] = reinterpret_cast<const float4 *>(xb[f])[NF / 4 - 1 - q];          // L[NF-4-4q .. NF-1-4q]
+            a[f] = reinterpret_cast<const float4 *>(xb[f] + LM_OFF)[q];                       // L[4q .. 4q+3]
+            b[f] = reinterpret_cast<const float4 *>(xb[f] + LM_OFF)[NF / 4 - 1 - q];          // L[NF-4-4q .. NF-1-4q]
         }
         const float d0 = tab->dct[(4 * q + 0) * 32 + li], d1 = tab->dct[(4 * q + 1) * 32 + li];
         const float d2 = tab->dct[(4 * q + 2) * 32 + li], d3 = tab->dct[(4 * q + 3) * 32 + li];

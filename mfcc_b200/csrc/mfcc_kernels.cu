@@ -54,7 +54,7 @@ using ShapeSmall = IntShape<8, 24, 4>;
 #define MFCC_F32_FT 32
 #endif
 #ifndef MFCC_F32_NFR
-#define MFCC_F32_NFR 2               // frames a warp carries through the chain together
+#define MFCC_F32_NFR 4               // frames a warp carries through the chain together (two per half-warp)
 #endif
 constexpr int WARPS_F   = MFCC_F32_WARPS;
 constexpr int THREADS_F = WARPS_F * 32;
@@ -131,7 +131,8 @@ struct Tile {
 // sample 8 before the tile's first frame, so every bulk copy is 16-byte aligned on both sides.
 static_assert((ShapeBig::FT * HOP) % 8 == 0 && (ShapeSmall::FT * HOP) % 8 == 0 && (FT_F * HOP) % 8 == 0,
               "tiles must start on 16-byte boundaries of the clip");
-static_assert(FT_F % (NFR_F * WARPS_F) == 0, "every frame a warp touches must lie inside the tile buffer");
+static_assert((NFR_F == 2 || NFR_F == 4) && FT_F % (NFR_F * WARPS_F) == 0, "every frame a warp touches must lie inside the tile buffer");
+static_assert(((FT_F / 2) * (HOP / 2)) % 32 == 16, "the two frames of a warp must lie 16 shared-memory banks apart");
 constexpr int OFF0 = 8;                                      // raw[OFF0] = first sample of the tile's first frame
 template <int FTT>
 __device__ __forceinline__ Tile tile_geo(const RunParams &p, long long ci, int ti) {
@@ -353,8 +354,7 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
     }
     // The padded power area has gaps no frame ever writes; the mel walk reads them with
     // zero weights, so they must hold finite numbers (0 * NaN would poison the sum).
-    for (int i = tid; i < WARPS_F * NFR_F * mfccf::PW_WORDS; i += THREADS_F)
-        (&sm->xbuf[0][0][0])[(i / mfccf::PW_WORDS) * mfccf::XWF + mfccf::PW_OFF + i % mfccf::PW_WORDS] = 0.0f;
+    for (int i = tid; i < WARPS_F * NFR_F * mfccf::XWF; i += THREADS_F) (&sm->xbuf[0][0][0])[i] = 0.0f;
     if (tid == 0) { mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1); }
     __syncthreads();
 
@@ -376,22 +376,29 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
         mbar_wait(&sm->mbar[buf], (uint32_t)(it >> 1) & 1u);
         __syncthreads();
         float *otile = static_cast<float *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
-        // a warp takes frames fl, fl + WARPS_F, ... NFR_F at a time; a frame past the end of the
-        // tile is computed on whatever the buffer holds and not stored
-        for (int fl = warp; fl < g.nf; fl += NFR_F * WARPS_F) {
-            const int16_t *fr[NFR_F];
-            float *xb[NFR_F];
+        // a warp takes NFR_F frames together: fl + HALF h + WARPS_F p for half-warp h (the samples of the
+        // two halves lie 16 banks apart), p = 0..NP-1; a frame past the end of the tile is computed on
+        // whatever the buffer holds and not stored
+        constexpr int HALF = FT_F / 2, NP = NFR_F / 2;
+        const int h = lane >> 4;
+        for (int fl = warp; fl < HALF && fl < g.nf; fl += NP * WARPS_F) {
+            const int16_t *fr[NP];
+            float *xh[NP], *xb[NFR_F];
 #pragma unroll
-            for (int f = 0; f < NFR_F; ++f) {
-                fr[f] = raw + OFF0 + HOP * (fl + f * WARPS_F);
-                xb[f] = sm->xbuf[warp][f];
+            for (int q = 0; q < NP; ++q) {
+                fr[q] = raw + OFF0 + HOP * (fl + HALF * h + WARPS_F * q);
+                xh[q] = sm->xbuf[warp][2 * q] + h * mfccf::XWF;
+                xb[2 * q] = sm->xbuf[warp][2 * q];
+                xb[2 * q + 1] = sm->xbuf[warp][2 * q + 1];
             }
             float c[NFR_F];
-            mfccf::power_warp_f32<NFR_F>(fr, xb, &sm->tab, lane);
+            mfccf::power_pair_f32<NP>(fr, xh, &sm->tab, lane);
             mfccf::cepstrum_warp_f32<NF, NFR_F>(xb, &sm->tab, lane, c);
 #pragma unroll
-            for (int f = 0; f < NFR_F; ++f)
-                if (lane < p.nceptrums && fl + f * WARPS_F < g.nf) otile[(fl + f * WARPS_F) * p.nceptrums + lane] = c[f];
+            for (int f = 0; f < NFR_F; ++f) {
+                const int fi = fl + HALF * (f & 1) + WARPS_F * (f >> 1);
+                if (lane < p.nceptrums && fi < g.nf) otile[fi * p.nceptrums + lane] = c[f];
+            }
         }
         __syncthreads();
     }
@@ -647,11 +654,13 @@ __global__ void __launch_bounds__(THREADS) mfcc_int_step(int16_t *state, const i
     }
 }
 
-// fp32 streaming step: same state layout as the integer mode (raw samples).
+// fp32 streaming step: same state layout as the integer mode (raw samples).  A warp takes two
+// streams, one per half-warp through the spectrum (power_pair_f32).
+constexpr int STEP_RAW_PITCH = NFFT + 32;       // halfwords; 272 words: the two rows lie 16 banks apart
 struct StepSmemF {
     mfccf::DevTablesF tab;
-    alignas(16) int16_t raw[WARPS][NFFT + 8];   // raw[w][1] = sample before the frame, frame from [2]
-    alignas(16) float xbuf[WARPS][mfccf::XWF];
+    alignas(16) int16_t raw[WARPS][2][STEP_RAW_PITCH];   // raw[w][h][1] = sample before the frame, frame from [2]
+    alignas(16) float xbuf[WARPS][2][mfccf::XWF];
 };
 
 template <int NF>
@@ -666,28 +675,41 @@ __global__ void __launch_bounds__(THREADS) mfcc_f32_step(int16_t *state, const i
         int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
         for (int i = tid; i < (int)(sizeof(mfccf::DevTablesF) / 16); i += THREADS) dst[i] = src[i];
     }
-    for (int i = tid; i < WARPS * mfccf::PW_WORDS; i += THREADS)      // see mfcc_f32_fused
-        sm->xbuf[i / mfccf::PW_WORDS][mfccf::PW_OFF + i % mfccf::PW_WORDS] = 0.0f;
+    for (int i = tid; i < WARPS * 2 * mfccf::XWF; i += THREADS) (&sm->xbuf[0][0][0])[i] = 0.0f;      // see mfcc_f32_fused
     __syncthreads();
     constexpr int HIST = NFFT - HOP;                      // 342
-    for (int s = blockIdx.x * WARPS + warp; s < n_streams; s += gridDim.x * WARPS) {
-        int16_t *st = state + (long long)s * STATE_N;     // st[0] = prev, st[1..342] = history
-        const int16_t *hp = hop + (long long)s * HOP;
-        int16_t *raw = sm->raw[warp];
-        // raw(n) for n = -1 .. 511 at raw[2 + n]
-        for (int i = lane; i <= NFFT; i += 32) {
-            const int n = i - 1;
-            raw[2 + n] = (n < HIST) ? st[1 + n] : hp[n - HIST];
+    const int h = lane >> 4;
+    for (int s0 = 2 * (blockIdx.x * WARPS + warp); s0 < n_streams; s0 += 2 * gridDim.x * WARPS) {
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+            const int s = s0 + f < n_streams ? s0 + f : s0;   // an odd last stream is computed twice, stored once
+            int16_t *st = state + (long long)s * STATE_N;     // st[0] = prev, st[1..342] = history
+            const int16_t *hp = hop + (long long)s * HOP;
+            int16_t *raw = sm->raw[warp][f];
+            // raw(n) for n = -1 .. 511 at raw[2 + n]
+            for (int i = lane; i <= NFFT; i += 32) {
+                const int n = i - 1;
+                raw[2 + n] = (n < HIST) ? st[1 + n] : hp[n - HIST];
+            }
         }
         __syncwarp();
         // new state = raw(HOP-1 .. 511)
-        for (int i = lane; i <= HIST; i += 32) st[i] = raw[2 + i + HOP - 1];
-        const int16_t *fr[1] = {raw + 2};
-        float *xb[1] = {sm->xbuf[warp]};
-        float c[1];
-        mfccf::power_warp_f32<1>(fr, xb, &sm->tab, lane);
-        mfccf::cepstrum_warp_f32<NF, 1>(xb, &sm->tab, lane, c);
-        if (lane < nceptrums) out[(long long)s * nceptrums + lane] = c[0];
+#pragma unroll
+        for (int f = 0; f < 2; ++f)
+            if (s0 + f < n_streams) {
+                int16_t *st = state + (long long)(s0 + f) * STATE_N;
+                for (int i = lane; i <= HIST; i += 32) st[i] = sm->raw[warp][f][2 + i + HOP - 1];
+            }
+        float *xb[2] = {sm->xbuf[warp][0], sm->xbuf[warp][1]};
+        float c[2];
+        const int16_t *fr[1] = {sm->raw[warp][0] + h * STEP_RAW_PITCH + 2};
+        float *xh[1] = {sm->xbuf[warp][0] + h * mfccf::XWF};
+        mfccf::power_pair_f32<1>(fr, xh, &sm->tab, lane);
+        mfccf::cepstrum_warp_f32<NF, 2>(xb, &sm->tab, lane, c);
+#pragma unroll
+        for (int f = 0; f < 2; ++f)
+            if (lane < nceptrums && s0 + f < n_streams) out[(long long)(s0 + f) * nceptrums + lane] = c[f];
+        __syncwarp();
     }
 }
 
@@ -716,7 +738,7 @@ struct HostPipe {
     cudaEvent_t ev_out[HOST_SLOTS_MAX] = {nullptr};   // d_out[slot] has left for the host
     size_t in_cap = 0, out_cap = 0;
     int slots_alloc = 0;
-    long long chunk_bytes = 32LL << 20;               // samples per chunk (mfcc_b200_host_config)
+    long long chunk_bytes = 16LL << 20;               // samples per chunk (mfcc_b200_host_config)
     int slots = 4;
     int fail_at_chunk = -1;                           // test hook: mfcc_b200_debug_fail_chunk
 };
@@ -846,13 +868,10 @@ int build_tables_f(const mfcc_b200_cfg &c, mfccf::DevTablesF &t) {
     const double PI = 3.14159265358979323846;
     const int nf = c.nfilters, nb = mfccf::NBINS1;
     const int maxseg = (nf == 32) ? 21 : 42;
-    for (int n = 0; n < NFFT; ++n) t.window[n] = c.f_window[n] * (1.0f / 32.0f);   // see emph_win()
-    for (int k1 = 0; k1 < 8; ++k1)
-        for (int l = 0; l < 32; ++l)
-            t.twA[k1 * 32 + l] = make_float2((float)cos(2 * PI * (l * k1) / 256), (float)-sin(2 * PI * (l * k1) / 256));
-    for (int p = 0; p < 8; ++p)
-        for (int cc = 0; cc < 4; ++cc)
-            t.twB[p * 4 + cc] = make_float2((float)cos(2 * PI * (cc * p) / 32), (float)-sin(2 * PI * (cc * p) / 32));
+    for (int n = 0; n < NFFT; ++n) t.window[n] = c.f_window[n];
+    for (int k2 = 0; k2 < 16; ++k2)
+        for (int n1 = 0; n1 < 16; ++n1)
+            t.tw16[k2 * 16 + n1] = make_float2((float)cos(2 * PI * (n1 * k2) / 256), (float)-sin(2 * PI * (n1 * k2) / 256));
     for (int k = 0; k <= 128; ++k)
         t.tw512[k] = make_float2((float)cos(2 * PI * k / 512), (float)-sin(2 * PI * k / 512));
     // DCT: the kernel uses D[k][nf-1-n] = (-1)^k D[k][n]; check it on the matrix we were given
@@ -915,6 +934,11 @@ int build_tables_f(const mfcc_b200_cfg &c, mfccf::DevTablesF &t) {
         if (g == 0) t.melw[j * nf + 0] = make_float2(0.0f, rise);              // rise of filter 0, in the fall slot
         else t.melw[((g == 1 ? len[0] : 0) + j) * nf + (g - 1)] = make_float2(rise, fall);
     }
+    for (int k1 = 0; k1 < 8; ++k1)
+        for (int l = 0; l < 16; ++l) {
+            const int k = 16 * k1 + l;
+            t.pst[k1 * 16 + l] = (uint32_t)t.paddr[k] | ((uint32_t)t.paddr[256 - k] << 16);
+        }
     t.mel_floor = c.f_mel_floor > 0.0f ? c.f_mel_floor : 0.0f;
     // the kernel's mel walk drops the lower half-warp after MEL_J0 steps when it has nothing left
     t.mel_tail_lane = 16;
@@ -1320,7 +1344,8 @@ int mfcc_b200_step(void *handle, void *d_state, const int16_t *d_hop, int32_t n_
     if (n_streams < 0) return fail(MFCC_B200_EINVAL, "negative size");
     if (n_streams == 0) return MFCC_B200_OK;
     if (!d_state || !d_hop || !d_out) return fail(MFCC_B200_EINVAL, "null buffer");
-    int grid = (n_streams + WARPS - 1) / WARPS;
+    const bool f32s = h->cfg.mode == MFCC_B200_MODE_FP32;      // the fp32 kernel takes two streams per warp
+    int grid = f32s ? (n_streams + 2 * WARPS - 1) / (2 * WARPS) : (n_streams + WARPS - 1) / WARPS;
     const int cap = h->sm_count * 8;
     if (grid > cap) grid = cap;
     cudaStream_t s = static_cast<cudaStream_t>(stream);

@@ -85,3 +85,70 @@ def test_mel_padded_layout_is_conflict_free(nf):
     # the power stores (lane handles bins lane + 32 i) stay cheap
     worst = max(LM.bank_conflict_degree(paddr[np.arange(32) + 32 * i]) for i in range(8))
     assert worst <= 2
+
+
+# ---- fp32 mode: index plan of power_pair_f32 (mfcc_f32.cuh) ------------------------------
+def test_f32_half_warp_plan():
+    """The 16 x 16 decomposition of the packed 256-point transform, the register order fft16
+    leaves (k16 / j16), the transposed exchange and the mirror-lane pairing of the real-input
+    split (lane l takes its k1 = 0..7 and receives registers 8..15 of lane 16 - l; lane 0 mirrors
+    itself one register further round), emulated lane by lane against numpy's FFT."""
+    def brev3(v):
+        return ((v & 1) << 2) | (v & 2) | ((v & 4) >> 2)
+
+    def k16(j):
+        return 2 * brev3(j) if j < 8 else 2 * brev3(j - 8) + 1
+
+    def j16(k):
+        return 8 + brev3(k >> 1) if k & 1 else brev3(k >> 1)
+
+    def fft8(v):
+        X = np.fft.fft(np.array(v))
+        return [X[brev3(j)] for j in range(8)]
+
+    def fft16(v):
+        e = [v[i] + v[i + 8] for i in range(8)]
+        o = [(v[i] - v[i + 8]) * np.exp(-2j * np.pi * i / 16) for i in range(8)]
+        return fft8(e) + fft8(o)
+
+    assert all(k16(j16(k)) == k for k in range(16))
+    rng=np.random.default_rng(0)
+    y=rng.standard_normal(512)
+    z=y[0::2]+1j*y[1::2]
+    # pass 1
+    T=np.zeros((16,16),complex)
+    for l in range(16):
+        v=[z[l+16*a] for a in range(16)]
+        v=fft16(v)
+        for j in range(16):
+            k2=k16(j)
+            T[k2][l]=v[j]*np.exp(-2j*np.pi*l*k2/256)
+    V=[]
+    for l in range(16):
+        v=[T[l][n1] for n1 in range(16)]
+        V.append(fft16(v))
+    Z=np.fft.fft(z)
+    for l in range(16):
+        for k1 in range(16):
+            assert abs(V[l][j16(k1)]-Z[16*k1+l])<1e-9
+    # mirror + split
+    X=np.fft.fft(y)[:257]
+    P=np.zeros(257)
+    for l in range(16):
+        src=(16-l)&15
+        r=[]
+        for i in range(8):
+            # value that lane src sends
+            ls=src
+            s=V[ls][j16(8+i)] if ls!=0 else V[ls][j16((9+i)&15)]
+            r.append(s)
+        for k1 in range(8):
+            k=16*k1+l
+            w=np.exp(-2j*np.pi*k/512)
+            A=V[l][j16(k1)]; B=r[7-k1]
+            F=0.5*(A+np.conj(B)); G=(A-np.conj(B))/(2j)
+            X0=F+w*G; X1=np.conj(F-w*G)
+            P[k]=abs(X0)**2; P[256-k]=abs(X1)**2
+        if l==0:
+            A=V[0][j16(8)]; P[128]=abs(A)**2
+    assert np.abs(P - np.abs(X) ** 2).max() < 1e-9
