@@ -104,6 +104,41 @@ __device__ __forceinline__ void bf_pk(int x0r, int x0i, int x1r, int x1i, int w2
     bf_pk(x0r, x0i, x1r, x1i, w2r, w2i, -w2i, p0, p1);
 }
 
+// ---------------------------------------------------------------------------------
+// The same butterfly on operands in "top-half form": the 16-bit value sits in bits 16..31 of a
+// 32-bit word and the low half is don't-care -- which is what the sums s0, s1 above already are,
+// and what the imaginary part of a packed (re | im << 16) exchange word is.  With
+//   d = (x0 << 16) + 32764 = (S0 & 0xffff0000) | 0x7ffc        (one LOP3; from a packed word's
+//                                                               real half: one PRMT)
+//   c = d >> 1             = (x0 << 15) + 16382                (one shift)
+// the two sums are  s0 = c + 2P  (the two multiply-adds, chained onto c)  and, because
+// s0 + s1 = (x0 << 16) + 32766,  s1 = d + 2 - s0  (one three-input add).  Twelve instructions
+// with the two shifts that turn x1 into a multiplicand, against fourteen for the form above;
+// no value is ever unpacked into a sign-extended integer unless it is multiplied.
+#ifndef MFCC_BF_SFORM
+#define MFCC_BF_SFORM 1
+#endif
+__device__ __forceinline__ unsigned d_of_top(unsigned S) { return (S & 0xffff0000u) | 0x7ffcu; }
+__device__ __forceinline__ unsigned d_of_lo16(unsigned w) { return __byte_perm(w, 0x7ffcu, 0x1054); }   // real half of a packed word
+__device__ __forceinline__ unsigned c_of_d(unsigned d) { return (unsigned)((int)d >> 1); }
+
+// x0 given as (dr, di), x1 as sign-extended integers; returns the four sums
+__device__ __forceinline__ Bf bf_d(unsigned dr, unsigned di, int x1r, int x1i, int w2r, int w2i, int nw2i) {
+    Bf o;
+    o.s0r = c_of_d(dr) + (unsigned)(x1r * w2r);
+    o.s0r += (unsigned)(x1i * nw2i);
+    o.s0i = c_of_d(di) + (unsigned)(x1i * w2r);
+    o.s0i += (unsigned)(x1r * w2i);
+    o.s1r = dr + 2u - o.s0r;
+    o.s1i = di + 2u - o.s0i;
+    return o;
+}
+// in place on top-half-form operands
+__device__ __forceinline__ void bf_s(unsigned &S0r, unsigned &S0i, unsigned &S1r, unsigned &S1i, int w2r, int w2i, int nw2i) {
+    const Bf o = bf_d(d_of_top(S0r), d_of_top(S0i), (int)S1r >> 16, (int)S1i >> 16, w2r, w2i, nw2i);
+    S0r = o.s0r; S0i = o.s0i; S1r = o.s1r; S1i = o.s1i;
+}
+
 // Trivial twiddles.  For tw = (16384, 0) the RTL's t = (x1 * 16384 + 8191) >> 14 is x1
 // itself, for tw = (0, -16384) it is (x1.im, -x1.re) (fft.py:93-96, :152-180; SURVEY.md
 // a5), so the butterfly is y = (x0 +- t) >> 1.  The sum of two 16-bit values halved
@@ -179,6 +214,72 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
     __syncwarp();
     // ---- pass B: lane (h, l4) takes positions 256h + 16m + l4, m = 0..15
     const int h = lane >> 4, l4 = lane & 15;
+#if MFCC_BF_SFORM
+    // stage s pairs m, m + 2^(s-4); twiddle index ((m mod 2^(s-4))*16 + l4) * (256 >> s).
+    // Indices >= 128 are the stored entry turned by -j: (re, im) -> (im, -re)  (fft.py:55-59)
+    unsigned sr[16], si[16];                 // top-half form
+    {   // stage 4: one twiddle per lane, operands straight from the packed exchange words
+        const int2 w = tab->twB[l4];
+        const int nwy = -w.y;
+#pragma unroll
+        for (int m = 0; m < 16; m += 2) {
+            const unsigned w0 = xbuf[xa_addr(16 * h + m, l4)], w1 = xbuf[xa_addr(16 * h + m + 1, l4)];
+            const Bf o = bf_d(d_of_lo16(w0), d_of_top(w0), lo16(w1), hi16(w1), w.x, w.y, nwy);
+            sr[m] = o.s0r; si[m] = o.s0i; sr[m + 1] = o.s1r; si[m + 1] = o.s1i;
+        }
+    }
+    __syncwarp();
+    {   // stage 5
+        const int2 w = tab->twB[16 + l4];
+        const int nwy = -w.y, nwx = -w.x;
+#pragma unroll
+        for (int m = 0; m < 16; m += 4) {
+            bf_s(sr[m], si[m], sr[m + 2], si[m + 2], w.x, w.y, nwy);
+            bf_s(sr[m + 1], si[m + 1], sr[m + 3], si[m + 3], w.y, nwx, w.x);    // W * (-j)
+        }
+    }
+    {   // stage 6
+#pragma unroll
+        for (int mm = 0; mm < 2; ++mm) {
+            const int2 w = tab->twB[32 + mm * 16 + l4];
+            const int nwy = -w.y, nwx = -w.x;
+#pragma unroll
+            for (int m = 0; m < 16; m += 8) {
+                bf_s(sr[m + mm], si[m + mm], sr[m + mm + 4], si[m + mm + 4], w.x, w.y, nwy);
+                bf_s(sr[m + mm + 2], si[m + mm + 2], sr[m + mm + 6], si[m + mm + 6], w.y, nwx, w.x);
+            }
+        }
+    }
+    {   // stage 7, packed into the exchange buffer at natural position + 16*(p >> 8)
+        unsigned *dst = xbuf + 272 * h + l4;
+#pragma unroll
+        for (int mm = 0; mm < 4; ++mm) {
+            const int2 w = tab->twB[64 + mm * 16 + l4];
+            bf_s(sr[mm], si[mm], sr[mm + 8], si[mm + 8], w.x, w.y, -w.y);
+            bf_s(sr[mm + 4], si[mm + 4], sr[mm + 12], si[mm + 12], w.y, -w.x, w.x);
+            dst[16 * mm] = __byte_perm(sr[mm], si[mm], 0x7632);
+            dst[16 * (mm + 8)] = __byte_perm(sr[mm + 8], si[mm + 8], 0x7632);
+            dst[16 * (mm + 4)] = __byte_perm(sr[mm + 4], si[mm + 4], 0x7632);
+            dst[16 * (mm + 12)] = __byte_perm(sr[mm + 12], si[mm + 12], 0x7632);
+        }
+    }
+    __syncwarp();
+    // ---- stage 8: only y0 is ever read (bins 0..255, fft_stream.py:24)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int b = lane + 32 * i;
+        const int2 w = tab->tw8[b];
+        const unsigned u0 = xbuf[b], u1 = xbuf[272 + b];
+        const int x1r = lo16(u1), x1i = hi16(u1);
+        unsigned s0r = c_of_d(d_of_lo16(u0)) + (unsigned)(x1r * w.x);
+        s0r -= (unsigned)(x1i * w.y);
+        unsigned s0i = c_of_d(d_of_top(u0)) + (unsigned)(x1i * w.x);
+        s0i += (unsigned)(x1r * w.y);
+        re[i] = (int)s0r >> 16;
+        im[i] = (int)s0i >> 16;
+    }
+    __syncwarp();   // xbuf may be reused by the caller
+#else
 #pragma unroll
     for (int m = 0; m < 16; ++m) {
         unsigned w = xbuf[xa_addr(16 * h + m, l4)];
@@ -241,6 +342,7 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
         im[i] = (int)(((unsigned)x0i << 15) + qi) >> 16;
     }
     __syncwarp();   // xbuf may be reused by the caller
+#endif
 }
 
 // ---------------------------------------------------------------------------------
@@ -369,7 +471,13 @@ __device__ __forceinline__ int dct_warp(unsigned L, const DevTables *tab, int la
         const unsigned x0 = up ? rc : p0;
         const unsigned x1 = up ? p1 : rc;
         const int2 w = tab->dct_tw[s * 32 + j];
+#if MFCC_BF_SFORM
+        const Bf o = bf_d(d_of_lo16(x0), d_of_top(x0), lo16(x1), hi16(x1), w.x, w.y, -w.y);
+        p0 = __byte_perm(o.s0r, o.s0i, 0x7632);
+        p1 = __byte_perm(o.s1r, o.s1i, 0x7632);
+#else
         bf_pk(lo16(x0), hi16(x0), lo16(x1), hi16(x1), w.x, w.y, p0, p1);
+#endif
     }
     const int2 w = tab->dct_twf[j];
     const unsigned q = (unsigned)(lo16(p0) * w.x) - (unsigned)(hi16(p0) * w.y) + 16382u;

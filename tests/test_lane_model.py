@@ -68,6 +68,33 @@ def test_trivial_butterflies_equal_the_general_one():
         assert np.array_equal(w_, LM.s16(g_)) and np.array_equal(g_, LM.s16(g_))
 
 
+def test_top_half_butterfly_equals_the_rtl_butterfly():
+    """bf_d / bf_s of mfcc_dev.cuh against the oracle's restatement of Butterfly
+    (mfcc/misc/fft.py:93-96, :188-191): every twiddle of the 512-point ROM, operands drawn from the
+    whole int16 range including the corners where the 16-bit wrap triggers, arbitrary junk in the
+    low halves of the operand words."""
+    from oracle import ref_np as R
+    rng = np.random.default_rng(5)
+    n = 20000
+    corners = np.array([-32768, -32767, -1, 0, 1, 32766, 32767])
+    for _ in range(4):
+        x = [np.concatenate([rng.integers(-32768, 32768, n), rng.choice(corners, n)]) for _ in range(4)]
+        k = rng.integers(0, 256, 2 * n)
+        tw = np.array([R.twiddle(512, int(i)) for i in range(256)])
+        wr, wi = tw[k, 0], tw[k, 1]
+        junk = [rng.integers(0, 65536, 2 * n) for _ in range(4)]
+        S = [((v & 0xFFFF) << 16) | j for v, j in zip(x, junk)]
+        s0r, s0i, s1r, s1i = LM.bfly_top_half(S[0], S[1], S[2], S[3], wr, wi)
+        got = [LM.s32(v) >> 16 for v in (s0r, s0i, s1r, s1i)]
+        want = LM.bfly(x[0], x[1], x[2], x[3], wr, wi)
+        for g, w in zip(got, want):
+            assert np.array_equal(g, w)
+        # and against the RTL restatement itself on a subset
+        for i in range(0, 2 * n, 997):
+            y = R.butterfly(int(x[0][i]), int(x[1][i]), int(x[2][i]), int(x[3][i]), int(wr[i]), int(wi[i]))
+            assert tuple(int(v) for v in y) == tuple(int(g[i]) for g in got)
+
+
 def test_log2_table_equals_the_loop():
     t = LM.log2_table()
     for m in list(range(0, 4200)) + list(range(60000, 65536)) + [32767, 32768, 16384, 9999]:
