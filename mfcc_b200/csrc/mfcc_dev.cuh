@@ -107,19 +107,40 @@ __device__ __forceinline__ void bf_pk(int x0r, int x0i, int x1r, int x1i, int w2
 // ---------------------------------------------------------------------------------
 // The same butterfly on operands in "top-half form": the 16-bit value sits in bits 16..31 of a
 // 32-bit word and the low half is don't-care -- which is what the sums s0, s1 above already are,
-// and what the imaginary part of a packed (re | im << 16) exchange word is.  With
-//   d = (x0 << 16) + 32764 = (S0 & 0xffff0000) | 0x7ffc        (one LOP3; from a packed word's
+// and what the imaginary part of a packed (re | im << 16) exchange word is.
+// (x0 << 15) + 2P is even, so the bias may be 16383 instead of 16382 without changing bit 16 and
+// up of s0 (an even number plus one never carries out of its low 16 bits).  With
+//   d = (x0 << 16) + 32767 = (S0 & 0xffff0000) | 0x7fff        (one LOP3; from a packed word's
 //                                                               real half: one PRMT)
-//   c = d >> 1             = (x0 << 15) + 16382                (one shift)
-// the two sums are  s0 = c + 2P  (the two multiply-adds, chained onto c)  and, because
-// s0 + s1 = (x0 << 16) + 32766,  s1 = d + 2 - s0  (one three-input add).  Twelve instructions
-// with the two shifts that turn x1 into a multiplicand, against fourteen for the form above;
-// no value is ever unpacked into a sign-extended integer unless it is multiplied.
+//   c = d >> 1             = (x0 << 15) + 16383                (one shift)
+// the sums are  s0' = c + 2P = s0 + 1  (the two multiply-adds, chained onto c)  and, because
+// s0 + s1 = (x0 << 16) + 32766,  s1 = d - s0'  exactly (one subtraction, written as a multiply-add
+// by -1 so that it runs on the multiplier pipe: the ALU pipe is the busier one in this kernel).
+// Twelve instructions with the two shifts that turn x1 into a multiplicand, against fourteen for
+// the form above; no value is unpacked into a sign-extended integer unless it is multiplied.
 #ifndef MFCC_BF_SFORM
 #define MFCC_BF_SFORM 1
 #endif
-__device__ __forceinline__ unsigned d_of_top(unsigned S) { return (S & 0xffff0000u) | 0x7ffcu; }
-__device__ __forceinline__ unsigned d_of_lo16(unsigned w) { return __byte_perm(w, 0x7ffcu, 0x1054); }   // real half of a packed word
+// (S & 0xffff0000) | 0x7fff as ONE lop3 (LUT 0xEA = (a & b) | c).  Written in PTX because the
+// optimiser otherwise turns the OR into an add and moves the constant down the chain, which costs
+// an extra add per component.
+__device__ __forceinline__ unsigned d_of_top(unsigned S) {
+    unsigned d;
+    asm("lop3.b32 %0, %1, 0xffff0000, 0x7fff, 0xEA;" : "=r"(d) : "r"(S));
+    return d;
+}
+// -v kept as a value of its own (the optimiser would rather negate a multiplicand per butterfly)
+__device__ __forceinline__ int neg_opaque(int v) {
+    int n;
+    asm("neg.s32 %0, %1;" : "=r"(n) : "r"(v));
+    return n;
+}
+__device__ __forceinline__ unsigned d_of_lo16(unsigned w) { return __byte_perm(w, 0x7fffu, 0x1054); }   // real half of a packed word
+__device__ __forceinline__ unsigned sub_on_fma(unsigned d, unsigned s) {      // d - s as mad.lo(s, -1, d)
+    unsigned r;
+    asm("mad.lo.u32 %0, %1, 0xffffffff, %2;" : "=r"(r) : "r"(s), "r"(d));
+    return r;
+}
 __device__ __forceinline__ unsigned c_of_d(unsigned d) { return (unsigned)((int)d >> 1); }
 
 // x0 given as (dr, di), x1 as sign-extended integers; returns the four sums
@@ -129,8 +150,8 @@ __device__ __forceinline__ Bf bf_d(unsigned dr, unsigned di, int x1r, int x1i, i
     o.s0r += (unsigned)(x1i * nw2i);
     o.s0i = c_of_d(di) + (unsigned)(x1i * w2r);
     o.s0i += (unsigned)(x1r * w2i);
-    o.s1r = dr + 2u - o.s0r;
-    o.s1i = di + 2u - o.s0i;
+    o.s1r = sub_on_fma(dr, o.s0r);
+    o.s1i = sub_on_fma(di, o.s0i);
     return o;
 }
 // in place on top-half-form operands
@@ -220,7 +241,7 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
     unsigned sr[16], si[16];                 // top-half form
     {   // stage 4: one twiddle per lane, operands straight from the packed exchange words
         const int2 w = tab->twB[l4];
-        const int nwy = -w.y;
+        const int nwy = neg_opaque(w.y);
 #pragma unroll
         for (int m = 0; m < 16; m += 2) {
             const unsigned w0 = xbuf[xa_addr(16 * h + m, l4)], w1 = xbuf[xa_addr(16 * h + m + 1, l4)];
@@ -231,7 +252,7 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
     __syncwarp();
     {   // stage 5
         const int2 w = tab->twB[16 + l4];
-        const int nwy = -w.y, nwx = -w.x;
+        const int nwy = neg_opaque(w.y), nwx = neg_opaque(w.x);
 #pragma unroll
         for (int m = 0; m < 16; m += 4) {
             bf_s(sr[m], si[m], sr[m + 2], si[m + 2], w.x, w.y, nwy);
@@ -242,7 +263,7 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
 #pragma unroll
         for (int mm = 0; mm < 2; ++mm) {
             const int2 w = tab->twB[32 + mm * 16 + l4];
-            const int nwy = -w.y, nwx = -w.x;
+            const int nwy = neg_opaque(w.y), nwx = neg_opaque(w.x);
 #pragma unroll
             for (int m = 0; m < 16; m += 8) {
                 bf_s(sr[m + mm], si[m + mm], sr[m + mm + 4], si[m + mm + 4], w.x, w.y, nwy);
@@ -255,8 +276,8 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
 #pragma unroll
         for (int mm = 0; mm < 4; ++mm) {
             const int2 w = tab->twB[64 + mm * 16 + l4];
-            bf_s(sr[mm], si[mm], sr[mm + 8], si[mm + 8], w.x, w.y, -w.y);
-            bf_s(sr[mm + 4], si[mm + 4], sr[mm + 12], si[mm + 12], w.y, -w.x, w.x);
+            bf_s(sr[mm], si[mm], sr[mm + 8], si[mm + 8], w.x, w.y, neg_opaque(w.y));
+            bf_s(sr[mm + 4], si[mm + 4], sr[mm + 12], si[mm + 12], w.y, neg_opaque(w.x), w.x);
             dst[16 * mm] = __byte_perm(sr[mm], si[mm], 0x7632);
             dst[16 * (mm + 8)] = __byte_perm(sr[mm + 8], si[mm + 8], 0x7632);
             dst[16 * (mm + 4)] = __byte_perm(sr[mm + 4], si[mm + 4], 0x7632);

@@ -51,19 +51,20 @@ def bfly(x0r, x0i, x1r, x1i, wr, wi):
 
 def bfly_top_half(S0r, S0i, S1r, S1i, wr, wi):
     """The butterfly on top-half-form operands (mfcc_dev.cuh: bf_d / bf_s): the value sits in
-    bits 16..31 of a 32-bit word, the low half is don't-care.  d = (x0 << 16) + 32764 is one
-    mask-and-or, c = d >> 1 = (x0 << 15) + 16382, s0 = c + 2P, s1 = d + 2 - s0.  Returns the four
-    sums as unsigned 32-bit words (results in their top halves)."""
+    bits 16..31 of a 32-bit word, the low half is don't-care.  d = (x0 << 16) + 32767 is one
+    mask-and-or, c = d >> 1 = (x0 << 15) + 16383, s0' = c + 2P (= s0 + 1: s0 is even, so its top
+    half does not change), s1 = d - s0'.  Returns the four sums as unsigned 32-bit words (results
+    in their top halves)."""
     U = 0xFFFFFFFF
     S0r, S0i, S1r, S1i = (np.asarray(v, dtype=np.int64) & U for v in (S0r, S0i, S1r, S1i))
     x1r, x1i = s32(S1r) >> 16, s32(S1i) >> 16
-    dr, di = (S0r & 0xFFFF0000) | 0x7FFC, (S0i & 0xFFFF0000) | 0x7FFC
+    dr, di = (S0r & 0xFFFF0000) | 0x7FFF, (S0i & 0xFFFF0000) | 0x7FFF
     cr, ci = s32(dr) >> 1, s32(di) >> 1
     w2r, w2i = 2 * wr, 2 * wi
     s0r = (cr + x1r * w2r - x1i * w2i) & U
     s0i = (ci + x1i * w2r + x1r * w2i) & U
-    s1r = (dr + 2 - s0r) & U
-    s1i = (di + 2 - s0i) & U
+    s1r = (dr - s0r) & U
+    s1i = (di - s0i) & U
     return s0r, s0i, s1r, s1i
 
 
