@@ -468,7 +468,18 @@ struct LrHandle {
     LrDev dev;
     std::vector<void *> allocs;
     LrDctParam *dct_param = nullptr;            // host copy of the DCT matrix for lr_dct_c (default shape only)
+    long long chunk_bytes = 1LL << 60;          // log-mel rows kept between the two passes (default: the whole batch)
     ~LrHandle() { delete dct_param; }
+    // clips per (log-mel, DCT) launch pair.  With chunks of ~48 MiB the rows written by lr_logmel are read
+    // back by the DCT kernel while they are still in L2 and the next chunk overwrites the same lines:
+    // measured 1499 -> 696 bytes of DRAM traffic per frame, but 8 % fewer frames/s (one persistent launch
+    // pair per 22 one-minute clips, each with its own tail), on a path that uses 7 % of the HBM
+    // bandwidth either way (profiles/r02_lr_chunks.txt).  So the default is one chunk.
+    long long chunk_clips(long long n_clips, long long n_frames) const {
+        long long per = chunk_bytes / (n_frames * n_mels * (long long)sizeof(float));
+        if (per < 1) per = 1;
+        return per < n_clips ? per : n_clips;
+    }
 };
 
 }  // namespace
@@ -661,11 +672,20 @@ int64_t mfcc_b200_librosa_frames(void *handle, int64_t n_samples)
 
 static int64_t lr_max_bytes(int32_t n_clips) { return (((int64_t)n_clips * 4) + 255) & ~(int64_t)255; }
 
+int mfcc_b200_librosa_config(void *handle, int64_t chunk_bytes)
+{
+    LrHandle *h = static_cast<LrHandle *>(handle);
+    if (!h || chunk_bytes < 0) return fail_ext(MFCC_B200_EINVAL, "bad argument");
+    if (chunk_bytes) h->chunk_bytes = chunk_bytes;
+    return MFCC_B200_OK;
+}
+
 int mfcc_b200_librosa_workspace(void *handle, int32_t n_clips, int64_t n_frames, int64_t *bytes)
 {
     LrHandle *h = static_cast<LrHandle *>(handle);
     if (!h || !bytes || n_clips < 0 || n_frames < 0) return fail_ext(MFCC_B200_EINVAL, "bad argument");
-    *bytes = lr_max_bytes(n_clips) + (int64_t)n_clips * n_frames * h->n_mels * (int64_t)sizeof(float);
+    const long long cc = n_frames ? h->chunk_clips(n_clips, n_frames) : 0;
+    *bytes = lr_max_bytes(n_clips) + cc * n_frames * h->n_mels * (int64_t)sizeof(float);
     return MFCC_B200_OK;
 }
 
@@ -687,33 +707,39 @@ int mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_stride,
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int *clipmax = static_cast<int *>(d_work);
     float *logmel = reinterpret_cast<float *>(static_cast<char *>(d_work) + lr_max_bytes(n_clips));
-    const long long total = (long long)n_clips * n_frames;
 
     lr_init_max<<<(n_clips + 255) / 256, 256, 0, st>>>(clipmax, n_clips);
     mfccb_host::count_launch();
-    long long g1 = (long long)h->sms * h->ctas1;
-    if (g1 > (total + LR_WARPS - 1) / LR_WARPS) g1 = (total + LR_WARPS - 1) / LR_WARPS;
-    h->logmel<<<(unsigned)g1, LR_THREADS, h->smem1, st>>>(d_x, clip_stride, n_samples, n_clips, n_frames, h->hop, h->center,
-                                                  h->n_mels, h->amin, h->dev, logmel, clipmax,
-                                                  taps ? taps->d_power : nullptr);
-    mfccb_host::count_launch();
     // float4 stores of whole rows: the output rows must be 16-byte aligned for lr_dct_c
     const bool rows16 = (reinterpret_cast<uintptr_t>(d_out) & 15) == 0 && (out_clip_stride % 4) == 0;
-    if (h->dct_param && rows16) {
-        long long g2 = (total + 32 * DC_WARPS - 1) / (32 * DC_WARPS);
-        if (g2 > (long long)h->sms * 3) g2 = (long long)h->sms * 3;
-        lr_dct_c<<<(unsigned)g2, DC_WARPS * 32, DC_WARPS * DC_MELS * DC_PITCH * sizeof(float), st>>>(
-            logmel, clipmax, total, n_frames, h->top_db, *h->dct_param, d_out, out_clip_stride);
-    } else {
-        long long g2 = (total + 31) / 32;
-        if (g2 > (long long)h->sms * 8) g2 = (long long)h->sms * 8;
-        const size_t dsm = ((((size_t)h->n_mels * h->n_mfcc + 3) & ~(size_t)3) + 8 * 4 * (size_t)h->n_mels) * sizeof(float);
-        lr_dct<<<(unsigned)g2, 256, dsm, st>>>(logmel, clipmax, n_clips, n_frames, h->n_mels, h->n_mfcc, h->top_db, h->dev,
-                                               d_out, out_clip_stride);
+    const long long cc = h->chunk_clips(n_clips, n_frames);
+    for (long long c0 = 0; c0 < n_clips; c0 += cc) {
+        const int nc = (int)((n_clips - c0) < cc ? (n_clips - c0) : cc);
+        const long long total = (long long)nc * n_frames;
+        const int16_t *x = d_x + c0 * clip_stride;
+        float *out = d_out + c0 * out_clip_stride;
+        long long g1 = (long long)h->sms * h->ctas1;
+        if (g1 > (total + LR_WARPS - 1) / LR_WARPS) g1 = (total + LR_WARPS - 1) / LR_WARPS;
+        h->logmel<<<(unsigned)g1, LR_THREADS, h->smem1, st>>>(x, clip_stride, n_samples, nc, n_frames, h->hop, h->center,
+                                                      h->n_mels, h->amin, h->dev, logmel, clipmax + c0,
+                                                      taps ? taps->d_power : nullptr);
+        mfccb_host::count_launch();
+        if (h->dct_param && rows16) {
+            long long g2 = (total + 32 * DC_WARPS - 1) / (32 * DC_WARPS);
+            if (g2 > (long long)h->sms * 3) g2 = (long long)h->sms * 3;
+            lr_dct_c<<<(unsigned)g2, DC_WARPS * 32, DC_WARPS * DC_MELS * DC_PITCH * sizeof(float), st>>>(
+                logmel, clipmax + c0, total, n_frames, h->top_db, *h->dct_param, out, out_clip_stride);
+        } else {
+            long long g2 = (total + 31) / 32;
+            if (g2 > (long long)h->sms * 8) g2 = (long long)h->sms * 8;
+            const size_t dsm = ((((size_t)h->n_mels * h->n_mfcc + 3) & ~(size_t)3) + 8 * 4 * (size_t)h->n_mels) * sizeof(float);
+            lr_dct<<<(unsigned)g2, 256, dsm, st>>>(logmel, clipmax + c0, nc, n_frames, h->n_mels, h->n_mfcc, h->top_db, h->dev,
+                                                   out, out_clip_stride);
+        }
+        mfccb_host::count_launch();
     }
-    mfccb_host::count_launch();
     if (taps && taps->d_logmel)
-        cudaMemcpyAsync(taps->d_logmel, logmel, (size_t)total * h->n_mels * sizeof(float), cudaMemcpyDeviceToDevice, st);
+        cudaMemcpyAsync(taps->d_logmel, logmel, (size_t)n_frames * h->n_mels * sizeof(float), cudaMemcpyDeviceToDevice, st);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail_ext(MFCC_B200_ECUDA, cudaGetErrorString(e));
     return MFCC_B200_OK;

@@ -61,6 +61,11 @@ class LibrosaMFCC:
         except Exception:       # interpreter shutdown: module globals may be gone
             pass
 
+    def config(self, chunk_mb):
+        """Size of the log-mel rows kept between the two passes (mfcc_b200_librosa_config)."""
+        _lib.check(_lib.lib().mfcc_b200_librosa_config(self._h, int(chunk_mb * (1 << 20))))
+        return self
+
     def num_frames(self, n_samples: int) -> int:
         """librosa's frame count: ``1 + n // hop_length`` for centred frames."""
         return int(_lib.lib().mfcc_b200_librosa_frames(self._h, n_samples))
