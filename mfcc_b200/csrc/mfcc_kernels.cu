@@ -324,7 +324,8 @@ struct SmemF {
     mfccf::DevTablesF tab;
     alignas(16) int16_t raw[2][RAWN_F];
     alignas(16) float xbuf[WARPS_F][NFR_F][mfccf::XWF];
-    alignas(8) uint64_t mbar[2];
+    alignas(8) uint64_t mbar[2];          // full[buf]: the tile's samples have arrived (one arrival + the copy's bytes)
+    alignas(8) uint64_t empty[2];         // empty[buf]: every warp is done with the tile in raw[buf] (WARPS_F arrivals)
 };
 
 static_assert(sizeof(SmemF) + 1024 <= 233472 / CTAS_PER_SM_F, "the fp32 kernel must keep CTAS_PER_SM_F CTAs resident");
@@ -355,26 +356,45 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
     // The padded power area has gaps no frame ever writes; the mel walk reads them with
     // zero weights, so they must hold finite numbers (0 * NaN would poison the sum).
     for (int i = tid; i < WARPS_F * NFR_F * mfccf::XWF; i += THREADS_F) (&sm->xbuf[0][0][0])[i] = 0.0f;
-    if (tid == 0) { mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1); }
+    if (tid == 0) {
+        mbar_init(&sm->mbar[0], 1); mbar_init(&sm->mbar[1], 1);
+        mbar_init(&sm->empty[0], WARPS_F); mbar_init(&sm->empty[1], WARPS_F);
+    }
     __syncthreads();
 
-    TileIter ti;
+    // No block-wide barrier in the tile loop.  Warp 0 is also the producer: before it starts tile i it
+    // waits until every warp has left tile i-1 (empty[]), fills what the bulk copy of tile i+1 does not
+    // cover (zeros before a clip, the ragged tail) and issues that copy into the buffer tile i-1 used.
+    // The other warps only ever wait for data (full[]), so the warps of a CTA drift up to a tile apart
+    // instead of meeting twice per tile.
+    TileIter ti, tn;
     ti.init(p);
-    if (tid == 0 && ti.tile < p.n_tiles) issue_tile_f(p, ti, sm, 0);
+    tn = ti;
+    auto produce = [&](const TileIter &t, int buf) {          // warp 0, all lanes
+        const Tile g = tile_geo<FT_F>(p, t.ci, t.ti);
+        int16_t *raw = sm->raw[buf];
+        for (int j = lane; j < g.lo; j += 32) raw[j] = 0;
+        for (int j = g.hi + lane; j < g.len; j += 32) {
+            const long long s = g.a0 + j;
+            raw[j] = (s >= 0 && s < p.n_samples) ? g.clip[s] : (int16_t)0;
+        }
+        __syncwarp();
+        if (lane == 0) issue_tile_f(p, t, sm, buf);           // its arrive releases the fills above
+    };
+    if (warp == 0 && tn.tile < p.n_tiles) produce(tn, 0);
+    tn.next();
     for (int it = 0; ti.tile < p.n_tiles; ++it) {
         const int buf = it & 1;
         const Tile g = tile_geo<FT_F>(p, ti.ci, ti.ti);
         ti.next();
-        int16_t *raw = sm->raw[buf];
-        for (int j = tid; j < g.lo; j += THREADS_F) raw[j] = 0;
-        for (int j = g.hi + tid; j < g.len; j += THREADS_F) {
-            const long long s = g.a0 + j;
-            raw[j] = (s >= 0 && s < p.n_samples) ? g.clip[s] : (int16_t)0;
+        const int16_t *raw = sm->raw[buf];
+        if (warp == 0 && tn.tile < p.n_tiles) {
+            // tile it+1 goes where tile it-1 was: completion (it-1)/2 of empty[buf^1]
+            if (it >= 1) mbar_wait(&sm->empty[buf ^ 1], (uint32_t)((it - 1) >> 1) & 1u);
+            produce(tn, buf ^ 1);
         }
-        // the other buffer was released by the barrier that ended the previous tile
-        if (tid == 0 && ti.tile < p.n_tiles) issue_tile_f(p, ti, sm, buf ^ 1);
+        tn.next();
         mbar_wait(&sm->mbar[buf], (uint32_t)(it >> 1) & 1u);
-        __syncthreads();
         float *otile = static_cast<float *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
         // a warp takes NFR_F frames together: fl + HALF h + WARPS_F p for half-warp h (the samples of the
         // two halves lie 16 banks apart), p = 0..NP-1; a frame past the end of the tile is computed on
@@ -400,7 +420,8 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
                 if (lane < p.nceptrums && fi < g.nf) otile[fi * p.nceptrums + lane] = c[f];
             }
         }
-        __syncthreads();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm->empty[buf]);
     }
 }
 
