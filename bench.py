@@ -533,7 +533,9 @@ def main():
         # per frame are constants of the build, measured once with ncu (profiles/collect.py);
         # the peak is the mixed IMAD/ALU issue rate profiles/micro/pipe_bench.cu measured
         try:
-            iss = json.load(open(os.path.join(ROOT, "profiles", "r01_issue.json")))
+            import glob
+            iss_path = sorted(glob.glob(os.path.join(ROOT, "profiles", "r[0-9][0-9]_issue.json")))[-1]   # latest round
+            iss = json.load(open(iss_path))
             k = iss["mfcc_int_fused"]
             lane_rate = k["warp_inst_per_frame"] * 32 * frames_rank / t_kernel_avg
             pk = iss["pipe_bench"]["mixed_lane_inst_per_s"]
@@ -542,7 +544,8 @@ def main():
                                                 "launch, scaled to this launch's frames" % k["dram_bytes_per_frame"])
             line["roofline"]["issue"] = {"achieved": lane_rate, "peak": pk, "unit": "lane-instr/s",
                                          "frac": lane_rate / pk, "warp_inst_per_frame": k["warp_inst_per_frame"],
-                                         "peak_source": "profiles/micro/pipe_bench.cu IMAD+SHF 1:1 on this GPU model"}
+                                         "peak_source": "profiles/micro/pipe_bench.cu IMAD+SHF 1:1 on this GPU model",
+                                         "counts_from": os.path.basename(iss_path)}
         except Exception:
             pass
         if e2e_sweep:

@@ -30,7 +30,7 @@ def main():
     global FRAMES
     tag = sys.argv[1]
     for suffix in ("bench_full.json", "bench_reference.json", "launches.csv", "pipe_bench.jsonl", "pytest.txt",
-                   "librosa_rate.txt", "accuracy.txt"):
+                   "librosa_rate.txt", "accuracy.txt", "smoke.txt", "stage_rates.txt", "mma_bench.jsonl"):
         src = os.path.join(G, "%s_%s" % (tag, suffix))
         if os.path.exists(src):
             shutil.copy(src, os.path.join(P, "%s_%s" % (tag, suffix)))
@@ -87,7 +87,7 @@ def main():
         issue["pipe_bench"] = {"device": rows[0], "imad_lane_inst_per_s": ops["IMAD (mad.lo.s32)"]["lane_inst_per_s"],
                                "mixed_lane_inst_per_s": ops["IMAD+SHF 1:1"]["lane_inst_per_s"],
                                "butterfly_mix_lane_inst_per_s": ops["IMAD:SHF:IADD 2:1:1"]["lane_inst_per_s"]}
-    json.dump(issue, open(os.path.join(P, "r01_issue.json"), "w"), indent=1)
+    json.dump(issue, open(os.path.join(P, "%s_issue.json" % tag.split("_")[0]), "w"), indent=1)
     print(json.dumps(issue, indent=1))
 
 

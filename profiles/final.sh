@@ -1,9 +1,10 @@
 #!/bin/bash
 # End-of-round measurement on the GPU box (run through gpurun):  bash profiles/final.sh <tag>
 # Everything it writes lands in gpurun_out/; profiles/collect.py turns that into the tracked summaries.
-tag=${1:-r01_c}
+tag=${1:-r02_b}
 o=gpurun_out
 python -m pytest tests -m gpu -q 2>&1 | tail -3 | tee $o/${tag}_pytest.txt
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -6 | tee $o/${tag}_smoke.txt
 python bench.py --impl reference > $o/${tag}_bench_reference.json 2> $o/${tag}_bench_reference.err
 python bench.py > $o/${tag}_bench_full.json 2> $o/${tag}_bench_full.err || tail -5 $o/${tag}_bench_full.err
 tail -c 600 $o/${tag}_bench_full.json
@@ -19,4 +20,6 @@ ncu --set full --import-source on --clock-control none -k regex:mfcc_f32_fused -
 ncu --set full --import-source on --clock-control none -k regex:lr_logmel -s 3 -c 1 -f -o $o/${tag}_lr python profiles/run_librosa.py 300 > /dev/null 2>&1
 python profiles/run_librosa.py 300 > $o/${tag}_librosa_rate.txt 2>/dev/null
 python profiles/accuracy.py > $o/${tag}_accuracy.txt 2>/dev/null
+python profiles/stage_rates.py 256 > $o/${tag}_stage_rates.txt 2>/dev/null
+[ -x profiles/micro/mma_bench ] && profiles/micro/mma_bench > $o/${tag}_mma_bench.jsonl
 ls -la $o | tail -12
