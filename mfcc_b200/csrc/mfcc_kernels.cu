@@ -97,7 +97,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "{\n"
         ".reg .pred p;\n"
         "MBAR_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n"
         "@p bra MBAR_DONE;\n"
         "bra MBAR_WAIT;\n"
         "MBAR_DONE:\n"
@@ -131,8 +131,8 @@ struct Tile {
 // sample 8 before the tile's first frame, so every bulk copy is 16-byte aligned on both sides.
 static_assert((ShapeBig::FT * HOP) % 8 == 0 && (ShapeSmall::FT * HOP) % 8 == 0 && (FT_F * HOP) % 8 == 0,
               "tiles must start on 16-byte boundaries of the clip");
-static_assert((NFR_F == 2 || NFR_F == 4) && FT_F % (NFR_F * WARPS_F) == 0, "every frame a warp touches must lie inside the tile buffer");
-static_assert(((FT_F / 2) * (HOP / 2)) % 32 == 16, "the two frames of a warp must lie 16 shared-memory banks apart");
+static_assert((NFR_F == 2 || NFR_F == 4) && FT_F == NFR_F * WARPS_F && FT_F % 32 == 0, "a tile is one pass of every warp over whole 32-frame blocks");
+static_assert((16 * (HOP / 2)) % 32 == 16, "frames 16 apart must lie 16 shared-memory banks apart");
 constexpr int OFF0 = 8;                                      // raw[OFF0] = first sample of the tile's first frame
 template <int FTT>
 __device__ __forceinline__ Tile tile_geo(const RunParams &p, long long ci, int ti) {
@@ -396,17 +396,22 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
         tn.next();
         mbar_wait(&sm->mbar[buf], (uint32_t)(it >> 1) & 1u);
         float *otile = static_cast<float *>(p.out) + g.ci * p.out_clip_stride + g.f0 * p.nceptrums;
-        // a warp takes NFR_F frames together: fl + HALF h + WARPS_F p for half-warp h (the samples of the
-        // two halves lie 16 banks apart), p = 0..NP-1; a frame past the end of the tile is computed on
-        // whatever the buffer holds and not stored
-        constexpr int HALF = FT_F / 2, NP = NFR_F / 2;
+        // a warp takes NFR_F frames together, two per half-warp: slot i = warp + WARPS_F q (q = 0..NP-1) is
+        // frame 32 (i / 16) + i % 16 for the lower half-warp and the frame 16 later for the upper one (their
+        // samples lie 16 banks apart); a frame past the end of the tile is computed on whatever the buffer
+        // holds and not stored
+        constexpr int NP = NFR_F / 2;
         const int h = lane >> 4;
-        for (int fl = warp; fl < HALF && fl < g.nf; fl += NP * WARPS_F) {
+        if (warp < g.nf) {
             const int16_t *fr[NP];
             float *xh[NP], *xb[NFR_F];
+            int fi[NFR_F];
 #pragma unroll
             for (int q = 0; q < NP; ++q) {
-                fr[q] = raw + OFF0 + HOP * (fl + HALF * h + WARPS_F * q);
+                const int i = warp + WARPS_F * q;
+                fi[2 * q] = 32 * (i >> 4) + (i & 15);
+                fi[2 * q + 1] = fi[2 * q] + 16;
+                fr[q] = raw + OFF0 + HOP * (fi[2 * q] + 16 * h);
                 xh[q] = sm->xbuf[warp][2 * q] + h * mfccf::XWF;
                 xb[2 * q] = sm->xbuf[warp][2 * q];
                 xb[2 * q + 1] = sm->xbuf[warp][2 * q + 1];
@@ -415,10 +420,8 @@ __global__ void __launch_bounds__(THREADS_F, CTAS_PER_SM_F) mfcc_f32_fused(const
             mfccf::power_pair_f32<NP>(fr, xh, &sm->tab, lane);
             mfccf::cepstrum_warp_f32<NF, NFR_F>(xb, &sm->tab, lane, c);
 #pragma unroll
-            for (int f = 0; f < NFR_F; ++f) {
-                const int fi = fl + HALF * (f & 1) + WARPS_F * (f >> 1);
-                if (lane < p.nceptrums && fi < g.nf) otile[fi * p.nceptrums + lane] = c[f];
-            }
+            for (int f = 0; f < NFR_F; ++f)
+                if (lane < p.nceptrums && fi[f] < g.nf) otile[fi[f] * p.nceptrums + lane] = c[f];
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm->empty[buf]);

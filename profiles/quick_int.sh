@@ -4,7 +4,7 @@ cp mfcc_b200/libmfcc_b200.so /tmp/libmfcc_b200.orig.so
 for v in build/variants/*.so; do
   echo "=== $v"
   cp $v mfcc_b200/libmfcc_b200.so
-  python -m pytest tests/test_gpu_parity.py tests/test_rtl_golden.py tests/test_hypothesis.py -m gpu -x -q 2>&1 | tail -1
+  python -m pytest tests/test_gpu_parity.py tests/test_rtl_golden.py tests/test_hypothesis.py tests/test_float_oracle.py -m gpu -x -q 2>&1 | tail -1
   python profiles/vbench.py 3000 10
   python profiles/vbench.py 3000 10
   ncu --metrics smsp__inst_executed.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,l1tex__data_pipe_lsu_wavefronts_mem_shared.sum,sm__inst_executed_pipe_alu.sum,sm__inst_executed_pipe_fmaheavy.sum,sm__inst_executed_pipe_fma.sum,sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active,sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_active,launch__registers_per_thread --clock-control none -k regex:fused -c 8 --csv --log-file gpurun_out/v_ncu.csv python profiles/run_both.py 300 > /dev/null 2>&1
