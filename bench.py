@@ -581,6 +581,15 @@ def main():
                                         "single_thread": {"value": v1, "sample": "16 clips x 60 s, %.1f s" % dt1},
                                         "checker_build": {"value": vc, "build_flags": "gcc -O2 -fopenmp",
                                                           "source": "oracle/mfcc_ref.c", "cores": thr}}
+                # the oracle as the checker of the timed launch itself: eight clips spread over the
+                # full-size batch (all four classes), bit for bit against the GPU result
+                idx = sorted({i for i in (0, 1, 2, 3, args.clips // 4 - 1, args.clips // 2 + 2, 3 * args.clips // 4 + 1,
+                                          args.clips - 1) if 0 <= i < args.clips})
+                it = torch.tensor(idx, device=dev)
+                want = RC.run(RC.RefConfig(nfilters=NFILT, nceptrums=NCEP), x[it].cpu().numpy(), threads=thr)
+                got = out[it].cpu().numpy()
+                line["cpu_baseline"]["spot_check"] = {"clips": idx, "frames": int(want.shape[0] * want.shape[1]),
+                                                      "bit_exact": bool((got == want).all())}
             except Exception as e:      # noqa: BLE001
                 line["cpu_baseline"] = {"value": None, "unit": "frames/s", "cores": 0, "kind": "port",
                                         "sample": "failed: %s: %s" % (type(e).__name__, e)}
