@@ -326,6 +326,10 @@ int     mfcc_b200_librosa_workspace(void *handle, int32_t n_clips, int64_t n_fra
  * chunk reuses the same lines: less than half the DRAM traffic and a workspace of that size, for
  * ~8 % fewer frames/s.  Changes what mfcc_b200_librosa_workspace returns. */
 int     mfcc_b200_librosa_config(void *handle, int64_t chunk_bytes);
+/* Default shape (128 mel bands, 32 coefficients) only: which kernel forms the DCT product. 1 (the
+ * default): warp-level tensor-core MMAs, TF32 with head/tail splits, float32-class accuracy;
+ * 0: the FMA-pipe kernel. */
+int     mfcc_b200_librosa_dct_path(void *handle, int32_t tensor_cores);
 int     mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t n_samples,
                               int32_t n_clips, int64_t n_frames, void *d_work, float *d_out,
                               int64_t out_clip_stride, const mfcc_b200_librosa_taps *taps, void *stream);

@@ -120,6 +120,8 @@ def lib():
     L.mfcc_b200_librosa_workspace.argtypes = [vp, i32, i64, C.POINTER(i64)]
     L.mfcc_b200_librosa_config.restype = C.c_int
     L.mfcc_b200_librosa_config.argtypes = [vp, i64]
+    L.mfcc_b200_librosa_dct_path.restype = C.c_int
+    L.mfcc_b200_librosa_dct_path.argtypes = [vp, i32]
     L.mfcc_b200_librosa_run.restype = C.c_int
     L.mfcc_b200_librosa_run.argtypes = [vp, vp, i64, i64, i32, i64, vp, vp, i64, C.POINTER(LibrosaTaps), vp]
     L.mfcc_b200_launch_count.restype = C.c_int64
@@ -138,7 +140,7 @@ EXPORTS = ["mfcc_b200_create", "mfcc_b200_destroy", "mfcc_b200_run", "mfcc_b200_
            "mfcc_b200_dct_stream", "mfcc_b200_power", "mfcc_b200_log2fix", "mfcc_b200_filterbank", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_step_host", "mfcc_b200_lifter",
            "mfcc_b200_standardize", "mfcc_b200_to_int16", "mfcc_b200_uart_frame", "mfcc_b200_vad_step",
            "mfcc_b200_librosa_create", "mfcc_b200_librosa_destroy", "mfcc_b200_librosa_frames",
-           "mfcc_b200_librosa_workspace", "mfcc_b200_librosa_config", "mfcc_b200_librosa_run",
+           "mfcc_b200_librosa_workspace", "mfcc_b200_librosa_config", "mfcc_b200_librosa_dct_path", "mfcc_b200_librosa_run",
            "mfcc_b200_launch_count", "mfcc_b200_last_error", "mfcc_b200_version"]
 
 

@@ -452,6 +452,113 @@ lr_dct_c(const float *__restrict__ logmel, const int *__restrict__ clipmax, long
     }
 }
 
+// The same product on the tensor cores (default shape: 128 mel bands, 32 coefficients):
+//   out[frames x 32] = max(logmel, floor)[frames x 128] . D[128 x 32]
+// as warp-level mma.sync.m16n8k8 TF32 with every operand split into a TF32 head and an fp32 tail
+// (x = hi + lo, hi = x with its 13 low mantissa bits cleared): hi.hi + lo.hi + hi.lo leaves a
+// relative error near 2^-21 per product, fp32 accumulation -- float32-class, checked against the
+// float64 restatement like the FMA kernels (tests/test_librosa_mode.py).  A warp takes 32 consecutive
+// frames (two 16-row tiles) and all 32 coefficients (four 8-column tiles): 16 k-steps x 4 x 2 x 3 =
+// 384 MMAs per 32 frames, 12 per frame (0.46 MMA per clock per SM measured,
+// profiles/micro/mma_bench.cu: 26 SM cycles per frame, about what the rows' 640 bytes take at the
+// HBM rate) against the 128 FFMA + 32 constant loads per frame of lr_dct_c.
+// A operands come straight from global memory, one 128-bit load per row and pair of k-steps: the k
+// index of an MMA is only summed over, so slot t of k-step 2S+e stands for band 16S + 4t + 2e and
+// slot t+4 for the next band, and the four lanes of a row read 64 contiguous bytes.  The B fragments
+// (the DCT matrix in that band order, head and tail) are built once per CTA in shared memory,
+// [k-step][column tile][lane], one 128-bit load per MMA triple.
+constexpr int DM_WARPS = 8;
+__device__ __forceinline__ float tf32_head(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const float (&a)[4], float b0, float b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
+                   "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+
+__global__ void __launch_bounds__(DM_WARPS * 32)
+lr_dct_mma(const float *__restrict__ logmel, const int *__restrict__ clipmax, long long total, long long n_frames,
+           float top_db, const float *__restrict__ D /* [128][32] */, float *__restrict__ out, long long out_clip_stride)
+{
+    extern __shared__ __align__(16) float4 bfrag[];            // [16 k-steps][4 column tiles][32 lanes]: (hi0, hi1, lo0, lo1)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    for (int i = threadIdx.x; i < 16 * 4 * 32; i += DM_WARPS * 32) {
+        const int ln = i & 31, j = (i >> 5) & 3, s = i >> 7;
+        const int band = 16 * (s >> 1) + 4 * (ln & 3) + 2 * (s & 1), col = 8 * j + (ln >> 2);
+        const float v0 = D[band * DC_MFCC + col], v1 = D[(band + 1) * DC_MFCC + col];
+        const float h0 = tf32_head(v0), h1 = tf32_head(v1);
+        bfrag[i] = make_float4(h0, h1, v0 - h0, v1 - h1);
+    }
+    __syncthreads();
+    const long long groups = (total + 31) / 32;
+    for (long long grp = (long long)blockIdx.x * DM_WARPS + warp; grp < groups; grp += (long long)gridDim.x * DM_WARPS) {
+        const long long item0 = grp * 32;
+        // lane j looks after frame j of the group: its clip, frame index and the dB floor of its clip
+        const long long my_item = item0 + lane < total ? item0 + lane : total - 1;
+        const long long my_clip = my_item / n_frames;
+        const long long my_f = my_item - my_clip * n_frames;
+        const float my_floor = top_db >= 0.0f ? key_float(clipmax[my_clip]) - top_db : -3.0e38f;
+        const float *rowp[4];                                   // rows g, g + 8, g + 16, g + 24 of the group
+        float rfloor[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int row = g + 8 * r;
+            const long long item = item0 + row < total ? item0 + row : total - 1;
+            rowp[r] = logmel + item * DC_MELS + 4 * t;
+            rfloor[r] = __shfl_sync(0xffffffffu, my_floor, row);
+        }
+        float acc[2][4][4];
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[m][j][0] = acc[m][j][1] = acc[m][j][2] = acc[m][j][3] = 0.0f;
+#pragma unroll 1
+        for (int S = 0; S < 8; ++S) {
+            float4 x[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                x[r] = *reinterpret_cast<const float4 *>(rowp[r] + 16 * S);
+                x[r].x = fmaxf(x[r].x, rfloor[r]); x[r].y = fmaxf(x[r].y, rfloor[r]);
+                x[r].z = fmaxf(x[r].z, rfloor[r]); x[r].w = fmaxf(x[r].w, rfloor[r]);
+            }
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                float ahi[2][4], alo[2][4];
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    // a0 (row g, slot t), a1 (row g + 8, slot t), a2 (row g, slot t + 4), a3 (row g + 8, slot t + 4)
+                    const float a[4] = {e ? x[2 * m].z : x[2 * m].x, e ? x[2 * m + 1].z : x[2 * m + 1].x,
+                                        e ? x[2 * m].w : x[2 * m].y, e ? x[2 * m + 1].w : x[2 * m + 1].y};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) { ahi[m][q] = tf32_head(a[q]); alo[m][q] = a[q] - ahi[m][q]; }
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 b = bfrag[((2 * S + e) * 4 + j) * 32 + lane];
+#pragma unroll
+                    for (int m = 0; m < 2; ++m) {
+                        mma_tf32(acc[m][j], ahi[m], b.x, b.y);
+                        mma_tf32(acc[m][j], alo[m], b.x, b.y);
+                        mma_tf32(acc[m][j], ahi[m], b.z, b.w);
+                    }
+                }
+            }
+        }
+        // c0, c1: row g, columns 8j + 2t, + 1; c2, c3: row g + 8
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int row = g + 8 * r;
+            const long long clip = __shfl_sync(0xffffffffu, my_clip, row), f = __shfl_sync(0xffffffffu, my_f, row);
+            if (item0 + row < total) {
+                float *o = out + clip * out_clip_stride + f * DC_MFCC + 2 * t;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    *reinterpret_cast<float2 *>(o + 8 * j) = make_float2(acc[r >> 1][j][2 * (r & 1)], acc[r >> 1][j][2 * (r & 1) + 1]);
+            }
+        }
+    }
+}
+
 __global__ void lr_init_max(int *clipmax, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) clipmax[i] = (int)0x80000000;
@@ -469,6 +576,7 @@ struct LrHandle {
     std::vector<void *> allocs;
     LrDctParam *dct_param = nullptr;            // host copy of the DCT matrix for lr_dct_c (default shape only)
     long long chunk_bytes = 1LL << 60;          // log-mel rows kept between the two passes (default: the whole batch)
+    int dct_tensor = 1;                         // default shape: DCT product by lr_dct_mma (0: lr_dct_c, FMA pipes)
     ~LrHandle() { delete dct_param; }
     // clips per (log-mel, DCT) launch pair.  With chunks of ~48 MiB the rows written by lr_logmel are read
     // back by the DCT kernel while they are still in L2 and the next chunk overwrites the same lines:
@@ -644,6 +752,8 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(lr_dct_c, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)(DC_WARPS * DC_MELS * DC_PITCH * sizeof(float)));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(lr_dct_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(16 * 4 * 32 * sizeof(float4)));
     }
     if (e != cudaSuccess) {
         for (void *p : h->allocs) cudaFree(p);
@@ -677,6 +787,14 @@ int mfcc_b200_librosa_config(void *handle, int64_t chunk_bytes)
     LrHandle *h = static_cast<LrHandle *>(handle);
     if (!h || chunk_bytes < 0) return fail_ext(MFCC_B200_EINVAL, "bad argument");
     if (chunk_bytes) h->chunk_bytes = chunk_bytes;
+    return MFCC_B200_OK;
+}
+
+int mfcc_b200_librosa_dct_path(void *handle, int32_t tensor_cores)
+{
+    LrHandle *h = static_cast<LrHandle *>(handle);
+    if (!h) return fail_ext(MFCC_B200_EINVAL, "null handle");
+    h->dct_tensor = tensor_cores ? 1 : 0;
     return MFCC_B200_OK;
 }
 
@@ -724,7 +842,12 @@ int mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_stride,
                                                       h->n_mels, h->amin, h->dev, logmel, clipmax + c0,
                                                       taps ? taps->d_power : nullptr);
         mfccb_host::count_launch();
-        if (h->dct_param && rows16) {
+        if (h->dct_param && rows16 && h->dct_tensor) {
+            long long g2 = (total + 32 * DM_WARPS - 1) / (32 * DM_WARPS);
+            if (g2 > (long long)h->sms * 2) g2 = (long long)h->sms * 2;
+            lr_dct_mma<<<(unsigned)g2, DM_WARPS * 32, 16 * 4 * 32 * sizeof(float4), st>>>(
+                logmel, clipmax + c0, total, n_frames, h->top_db, h->dev.dct, out, out_clip_stride);
+        } else if (h->dct_param && rows16) {
             long long g2 = (total + 32 * DC_WARPS - 1) / (32 * DC_WARPS);
             if (g2 > (long long)h->sms * 3) g2 = (long long)h->sms * 3;
             lr_dct_c<<<(unsigned)g2, DC_WARPS * 32, DC_WARPS * DC_MELS * DC_PITCH * sizeof(float), st>>>(

@@ -66,6 +66,11 @@ class LibrosaMFCC:
         _lib.check(_lib.lib().mfcc_b200_librosa_config(self._h, int(chunk_mb * (1 << 20))))
         return self
 
+    def dct_path(self, tensor_cores=True):
+        """Default shape only: DCT product on the tensor cores (default) or on the FMA pipes."""
+        _lib.check(_lib.lib().mfcc_b200_librosa_dct_path(self._h, 1 if tensor_cores else 0))
+        return self
+
     def num_frames(self, n_samples: int) -> int:
         """librosa's frame count: ``1 + n // hop_length`` for centred frames."""
         return int(_lib.lib().mfcc_b200_librosa_frames(self._h, n_samples))

@@ -103,6 +103,38 @@ def test_cuda_librosa_batch_short_clips_and_silence(wav):
 
 
 @pytest.mark.gpu
+def test_cuda_librosa_dct_on_tensor_cores_and_on_fma_pipes(wav):
+    """The default shape forms the DCT product with tensor-core MMAs (TF32 with head / tail splits,
+    lr_dct_mma); the FMA-pipe kernel lr_dct_c stays selectable.  Both against the float64
+    restatement inside the stated tolerance, on a batch whose frame count is not a multiple of the
+    32-frame group (ragged last group, rows of two clips in one group, a silent clip whose rows sit
+    at the dB floor), and close to each other at float32 resolution."""
+    import torch
+    import mfcc_b200
+    op = mfcc_b200.LibrosaMFCC(device="cuda:0")
+    rng = np.random.default_rng(3)
+    n = 170 * 45 + 13                                            # 46 frames per clip
+    x = np.stack([wav[30000:30000 + n], np.clip(rng.normal(0, 3000, n), -32768, 32767).astype(np.int16),
+                  np.zeros(n, dtype=np.int16), wav[90000:90000 + n],
+                  (8000 * np.sin(np.arange(n) * 0.3)).astype(np.int16)])
+    xd = torch.from_numpy(x).to("cuda:0")
+    got = {}
+    for tc in (True, False):
+        op.dct_path(tc)
+        got[tc] = op(xd).cpu().numpy()
+        assert got[tc].shape == (5, 46, 32)
+        for i in (0, 1, 3, 4):
+            _close(got[tc][i], L.mfcc(x[i]))
+        assert np.allclose(got[tc][2][:, 0], -100.0 * np.sqrt(128.0), atol=1e-2)
+    op.dct_path(True)
+    scale = np.abs(got[False]).max()
+    assert np.abs(got[True] - got[False]).max() <= 2e-5 * scale
+    # pitched output rows and a single clip through the same kernel
+    one = op(xd[0]).cpu().numpy()
+    assert np.array_equal(one, got[True][0])
+
+
+@pytest.mark.gpu
 def test_cuda_librosa_other_sizes_and_scale_chain(wav):
     import torch
     import mfcc_b200
