@@ -334,6 +334,28 @@ int     mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_str
                               int32_t n_clips, int64_t n_frames, void *d_work, float *d_out,
                               int64_t out_clip_stride, const mfcc_b200_librosa_taps *taps, void *stream);
 
+/*
+ * No counterpart in the reference: added for callers that
+ * cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  mfcc_b200_librosa_run without the workspace argument: the per-clip maxima
+ * and the log-mel rows between the two passes live in a file-scope static __device__ array of
+ * MFCC_B200_LIBROSA_STATIC_BYTES (16 MiB; every GPU that loads the library holds it until the
+ * process exits).  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library
+ * routine); the array's device address was taken once, at mfcc_b200_librosa_create, on the device
+ * that was current then, which must be current again here.  Limit:
+ *     n_clips * n_frames * n_mels * 4 + round_up(4 * n_clips, 256) <= MFCC_B200_LIBROSA_STATIC_BYTES
+ * (about 32 700 frames of 128 bands per call: five one-minute clips); anything larger is
+ * rejected with MFCC_B200_EINVAL and a message that says so.  Same kernels and the same results
+ * as mfcc_b200_librosa_run; no taps.  ALL calls on a device share the one array (it keeps the last
+ * call's contents; what must start clean is cleared by the call itself): calls that overlap on
+ * the GPU -- different streams, different handles, different host threads -- race.  Serialise
+ * them on one stream.
+ */
+#define MFCC_B200_LIBROSA_STATIC_BYTES (16 * 1024 * 1024)
+int     mfcc_b200_librosa_run_static(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t n_samples,
+                                     int32_t n_clips, int64_t n_frames, float *d_out, int64_t out_clip_stride,
+                                     void *stream);
+
 /* Number of kernels this library has launched since it was loaded (bench.py's
  * gpu_launches). */
 int64_t     mfcc_b200_launch_count(void);

@@ -124,6 +124,8 @@ def lib():
     L.mfcc_b200_librosa_dct_path.argtypes = [vp, i32]
     L.mfcc_b200_librosa_run.restype = C.c_int
     L.mfcc_b200_librosa_run.argtypes = [vp, vp, i64, i64, i32, i64, vp, vp, i64, C.POINTER(LibrosaTaps), vp]
+    L.mfcc_b200_librosa_run_static.restype = C.c_int
+    L.mfcc_b200_librosa_run_static.argtypes = [vp, vp, i64, i64, i32, i64, vp, i64, vp]
     L.mfcc_b200_launch_count.restype = C.c_int64
     L.mfcc_b200_launch_count.argtypes = []
     L.mfcc_b200_last_error.restype = C.c_char_p
@@ -140,8 +142,11 @@ EXPORTS = ["mfcc_b200_create", "mfcc_b200_destroy", "mfcc_b200_run", "mfcc_b200_
            "mfcc_b200_dct_stream", "mfcc_b200_power", "mfcc_b200_log2fix", "mfcc_b200_filterbank", "mfcc_b200_state_bytes", "mfcc_b200_step", "mfcc_b200_step_host", "mfcc_b200_lifter",
            "mfcc_b200_standardize", "mfcc_b200_to_int16", "mfcc_b200_uart_frame", "mfcc_b200_vad_step",
            "mfcc_b200_librosa_create", "mfcc_b200_librosa_destroy", "mfcc_b200_librosa_frames",
-           "mfcc_b200_librosa_workspace", "mfcc_b200_librosa_config", "mfcc_b200_librosa_dct_path", "mfcc_b200_librosa_run",
+           "mfcc_b200_librosa_workspace", "mfcc_b200_librosa_config", "mfcc_b200_librosa_dct_path", "mfcc_b200_librosa_run", "mfcc_b200_librosa_run_static",
            "mfcc_b200_launch_count", "mfcc_b200_last_error", "mfcc_b200_version"]
+
+
+LIBROSA_STATIC_BYTES = 16 * 1024 * 1024       # MFCC_B200_LIBROSA_STATIC_BYTES
 
 
 def check(rc):

@@ -24,6 +24,13 @@
 
 #include "../../include/mfcc_b200.h"
 
+// Scratch of mfcc_b200_librosa_run_static (the entry point that allocates nothing): per-clip
+// maxima + log-mel rows of one call.  Every GPU that loads the library holds these bytes until
+// the process exits.  In host code this name is a stand-in, not a device address: the address
+// comes from cudaGetSymbolAddress (mfcc_b200_librosa_create, once per handle, with the handle's
+// device current).
+static __device__ __align__(256) unsigned char lr_static_scratch[MFCC_B200_LIBROSA_STATIC_BYTES];
+
 namespace mfccb_host {
 int fail_ext(int code, const char *msg);
 void count_launch();
@@ -577,6 +584,9 @@ struct LrHandle {
     LrDctParam *dct_param = nullptr;            // host copy of the DCT matrix for lr_dct_c (default shape only)
     long long chunk_bytes = 1LL << 60;          // log-mel rows kept between the two passes (default: the whole batch)
     int dct_tensor = 1;                         // default shape: DCT product by lr_dct_mma (0: lr_dct_c, FMA pipes)
+    void *static_scratch = nullptr;             // device address of lr_static_scratch on the handle's device
+    int device = -1;                            // the device the handle was created on
+    std::string static_err;                     // why static_scratch is null, if it is
     ~LrHandle() { delete dct_param; }
     // clips per (log-mel, DCT) launch pair.  With chunks of ~48 MiB the rows written by lr_logmel are read
     // back by the DCT kernel while they are still in L2 and the next chunk overwrites the same lines:
@@ -760,6 +770,15 @@ int mfcc_b200_librosa_create(const mfcc_b200_librosa_cfg *cfg, void **handle)
         delete h;
         return fail_ext(MFCC_B200_ECUDA, cudaGetErrorString(e));
     }
+    // set-up of mfcc_b200_librosa_run_static: the device address of the file-scope scratch array on
+    // THIS device (the current one).  A failure here does not fail create; the entry point reports it.
+    {
+        void *sp = nullptr;
+        cudaError_t es = cudaGetDevice(&h->device);
+        if (es == cudaSuccess) es = cudaGetSymbolAddress(&sp, lr_static_scratch);
+        if (es == cudaSuccess) h->static_scratch = sp;
+        else { h->static_err = cudaGetErrorString(es); cudaGetLastError(); }
+    }
     *handle = h;
     return MFCC_B200_OK;
 }
@@ -866,6 +885,43 @@ int mfcc_b200_librosa_run(void *handle, const int16_t *d_x, int64_t clip_stride,
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail_ext(MFCC_B200_ECUDA, cudaGetErrorString(e));
     return MFCC_B200_OK;
+}
+
+int mfcc_b200_librosa_run_static(void *handle, const int16_t *d_x, int64_t clip_stride, int64_t n_samples,
+                                 int32_t n_clips, int64_t n_frames, float *d_out, int64_t out_clip_stride, void *stream)
+{
+    LrHandle *h = static_cast<LrHandle *>(handle);
+    if (!h) return fail_ext(MFCC_B200_EINVAL, "null handle");
+    if (n_clips < 0 || n_frames < 0 || n_samples < 0) return fail_ext(MFCC_B200_EINVAL, "negative size");
+    if (!h->static_scratch) {
+        static thread_local std::string msg;
+        msg = "mfcc_b200_librosa_run_static: cudaGetSymbolAddress failed at create: " + h->static_err;
+        return fail_ext(MFCC_B200_ECUDA, msg.c_str());
+    }
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev != h->device)
+        return fail_ext(MFCC_B200_EINVAL, "mfcc_b200_librosa_run_static: the handle's device must be current");
+    // the whole batch in one chunk: maxima + rows must fit the static array (no overflow: sizes are
+    // bounded before they are multiplied)
+    const int64_t row_bytes = (int64_t)h->n_mels * (int64_t)sizeof(float);
+    const int64_t cap_rows = ((int64_t)MFCC_B200_LIBROSA_STATIC_BYTES - lr_max_bytes(n_clips)) / row_bytes;
+    if (n_clips > (int32_t)(MFCC_B200_LIBROSA_STATIC_BYTES / 8) || cap_rows < 0 ||
+        (n_clips > 0 && n_frames > cap_rows / n_clips)) {
+        static thread_local std::string msg;
+        msg = "mfcc_b200_librosa_run_static: " + std::to_string(n_clips) + " clips x " + std::to_string(n_frames) +
+              " frames need more than the " + std::to_string((long long)MFCC_B200_LIBROSA_STATIC_BYTES) +
+              " bytes of static scratch (n_clips * n_frames * n_mels * 4 + 256-byte-rounded 4 * n_clips); "
+              "use mfcc_b200_librosa_run with a caller-owned workspace";
+        return fail_ext(MFCC_B200_EINVAL, msg.c_str());
+    }
+    // same kernels as mfcc_b200_librosa_run, with the chunk covering the whole batch; lr_init_max clears
+    // the maxima (the only part of the scratch that must not carry over), every row is written before it is read
+    const long long keep = h->chunk_bytes;
+    h->chunk_bytes = 1LL << 60;
+    const int rc = mfcc_b200_librosa_run(handle, d_x, clip_stride, n_samples, n_clips, n_frames, h->static_scratch, d_out,
+                                         out_clip_stride, nullptr, stream);
+    h->chunk_bytes = keep;
+    return rc;
 }
 
 }  // extern "C"
