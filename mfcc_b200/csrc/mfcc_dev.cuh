@@ -20,6 +20,9 @@ constexpr int NBINS  = 256;      // FftStream emits bins 0..255, fft_stream.py:2
 constexpr int XW     = 656;      // 32-bit words of the per-warp exchange buffer
 constexpr unsigned FULL = 0xffffffffu;
 
+#ifndef MFCC_CURVE_VEC
+#define MFCC_CURVE_VEC 1
+#endif
 // Tables every CTA copies from global to shared memory once (16-byte multiples).
 struct alignas(16) DevTables {
     int2     twB[128];       // stages 4..7, doubled (2re, 2im): [16 | 16 | 32 | 64] entries
@@ -29,7 +32,13 @@ struct alignas(16) DevTables {
     alignas(16) uint16_t logfrac[2048];  // Log2Fix fraction bits 10..1 for every 12-bit mantissa: see log2fix_tab()
     int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
     int2     dct_twf[32];    // final DCT stage, lane j = bin j, doubled
+#if MFCC_CURVE_VEC
+    // window multipliers (9 bits, unsigned), window.py:59-115, as each lane of frame_warp needs them:
+    // [q][lane] = the multipliers of positions brev5(lane) + 32 brev4(l), l = 4q..4q+3 (curve_at() for position n)
+    uint32_t curveL[4 * 32 * 4];
+#else
     alignas(16) uint16_t curve[512];     // window multipliers (9 bits, unsigned), window.py:59-115
+#endif
     int16_t  seg_walk[40];   // word address (padded power layout) where lane's walk starts:
                              // segment lane+1, lane 0: segments 0 and 1
     int16_t  seg_close[40];  // closing bin of mel segment g
@@ -39,7 +48,8 @@ struct alignas(16) DevTables {
     uint4    pstore[2 * 32]; // [i / 4][lane]: paddr[lane + 32 i], i = 0..7: where the lane's power values go
     int32_t  mel_lo_bit;     // filterbank.py:122
     int32_t  nseg;
-    int32_t  pad[2];
+    int32_t  mel_onewide;    // 32 filters: melab holds (wa, nc) pairs, see mel_warp()
+    int32_t  pad[1];
 };
 static_assert(sizeof(DevTables) % 16 == 0, "DevTables must be int4-copyable");
 
@@ -52,6 +62,14 @@ constexpr int H_TWA_IM[8] = {0, -6270, -11585, -15137, -16384, -15137, -11585, -
 
 __host__ __device__ constexpr int brev4(int v) {
     return ((v & 1) << 3) | ((v & 2) << 1) | ((v & 4) >> 1) | ((v & 8) >> 3);
+}
+__host__ __device__ constexpr int brev5(int v) {
+    return ((v & 1) << 4) | ((v & 2) << 2) | (v & 4) | ((v & 8) >> 2) | ((v & 16) >> 4);
+}
+// window multiplier of sample position n (0..511) in either table layout
+__host__ __device__ __forceinline__ int curve_index(int n) {       // index into DevTables::curveL
+    const int lane = brev5(n & 31), l = brev4(n >> 5);
+    return ((l >> 2) * 32 + lane) * 4 + (l & 3);
 }
 
 // ---------------------------------------------------------------------------------
@@ -389,7 +407,31 @@ __device__ __forceinline__ unsigned mel_warp(const unsigned *pw, const DevTables
     const int li = lane & (NF - 1);
     const unsigned *p = pw + tab->seg_walk[li];
     unsigned long long a = 0, b = 0;
-    if (NF == 32) {
+    if (NF == 32 && tab->mel_onewide) {
+        // One 64-bit and one 32-bit multiply-add per bin instead of two 64-bit ones (IMAD.WIDE issues at
+        // half the rate of IMAD).  With nc = 1 on every bin of the segment and 0 on the padding,
+        // D = sum d nc (32 bits, wraps):  Bbar_g = ((D_nc + PK) << 30) - (A' + (PK << 30)) = (D << 30) - a,
+        // so the slice is taken from  a_{g-1} + (D_g << 30) - a_g;  only bits lo_bit .. lo_bit+15 < 62 are
+        // kept, for which (D mod 2^32) << 30 is exact.  Lane 0 walks segment 0 too: mfcc_b200_create()
+        // selects this form only when the non-closing weights of segment 0 are all zero (32-filter bank:
+        // bins 0..1, bin 0 weighs 0), so Abar_0 = PK_0 << 30 and that bin just counts into lane 0's D.
+        // tests/lane_model.py: mel_lanes_onewide.
+        const uint4 *wt = reinterpret_cast<const uint4 *>(tab->melab) + li;
+        unsigned D = 0;
+#pragma unroll
+        for (int jj = 0; jj < (MAXSEG + 1) / 2; ++jj) {
+            const unsigned d0 = p[2 * jj], d1 = p[2 * jj + 1];
+            const uint4 w = wt[jj * NF];
+            a += (unsigned long long)d0 * w.x;
+            D += d0 * w.y;
+            a += (unsigned long long)d1 * w.z;
+            D += d1 * w.w;
+        }
+        unsigned long long pa = __shfl_up_sync(FULL, a, 1);
+        if (li == 0) pa = 0;
+        const unsigned long long x = pa - a + ((unsigned long long)D << 30);
+        return (unsigned)(x >> tab->mel_lo_bit) & 0xffffu;
+    } else if (NF == 32) {
         // two steps per 128-bit weight load: melab as uint4 [step / 2][lane]
         const uint4 *wt = reinterpret_cast<const uint4 *>(tab->melab) + li;
 #pragma unroll

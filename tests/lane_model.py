@@ -244,6 +244,47 @@ def mel_lanes(pw, nfilters, samplerate=16e3, nfft=512, lo_bit=31):
     return out
 
 
+def mel_lanes_onewide(pw, nfilters, samplerate=16e3, nfft=512, lo_bit=31):
+    """mel_warp() in its one-wide-multiply form (32 filters): one 64-bit multiply-add and one 32-bit
+    one per step.  With wa the weight of a bin (2^30 on the closing bin) and nc = 1 on every bin of the
+    segment (0 on the zero padding), a = sum d*wa (64-bit), D = sum d*nc (32-bit, wraps):
+        Bbar_g = sum_{non-closing} d (2^30 - w) = ((D_nc + PK) << 30) - (A' + PK << 30) = (D << 30) - a
+    so the register the hardware slices is  Abar_{g-1} + Bbar_g = a_{g-1} + (D_g << 30) - a_g, of which
+    only bits lo_bit .. lo_bit+15 are kept: (D mod 2^32) << 30 is exact modulo 2^62.  Lane 0 walks
+    segment 0 first: usable when every non-closing weight of segment 0 is zero (true for the 32-filter
+    bank: segment 0 is bins 0..1 and bin 0 has weight 0), because then Abar_0 = PK_0 << 30 and the closing
+    bin of segment 0 simply counts into lane 0's D.  Returns None when the bank does not allow it."""
+    ab, bounds = mel_tables(nfilters, samplerate, nfft)
+    maxseg = ab.shape[0]
+    M64, M32 = (1 << 64) - 1, (1 << 32) - 1
+    paddr, walk, end = mel_padded_layout(nfilters, samplerate, nfft)
+    pwx = np.full(end + maxseg + 8, 12345, dtype=np.int64)
+    pwx[paddr] = np.asarray(pw, dtype=np.int64)
+    len0 = bounds[0][1] - bounds[0][0] + 1
+    if any(int(ab[j, 0, 1]) != 0 for j in range(len0 - 1)) or int(ab[len0 - 1, 0, 1]) != 1 << 30:
+        return None
+    a, D = [0] * nfilters, [0] * nfilters
+    for li in range(nfilters):
+        first = int(walk[li])
+        seglen = bounds[li + 1][1] - bounds[li + 1][0] + 1
+        for j in range(maxseg):
+            d = int(pwx[first + j])
+            if li == 0 and j < len0:
+                wa, nc = 0, (1 if j == len0 - 1 else 0)       # segment 0: only its closing bin counts, as d << 30
+            else:
+                jj = j - (len0 if li == 0 else 0)
+                inside = 0 <= jj < seglen
+                wa = int(ab[j, li, 0]) if inside else 0
+                nc = 1 if inside else 0
+            a[li] = (a[li] + d * wa) & M64
+            D[li] = (D[li] + d * nc) & M32
+    out = np.zeros(nfilters, dtype=np.int64)
+    for li in range(nfilters):
+        pa = 0 if li == 0 else a[li - 1]
+        out[li] = (((pa + (D[li] << 30) - a[li]) & M64) >> lo_bit) & 0xFFFF
+    return out
+
+
 def log2_table():
     """logfrac[] of DevTables: the ten squarings for every 12-bit mantissa."""
     t = np.zeros(2048, dtype=np.int64)

@@ -95,6 +95,24 @@ def test_top_half_butterfly_equals_the_rtl_butterfly():
             assert tuple(int(v) for v in y) == tuple(int(g[i]) for g in got)
 
 
+def test_mel_one_wide_multiply_form_equals_the_two_sum_form(nf=32, lo=31):
+    """mel_warp's MFCC_MEL_ONEWIDE form (one 64-bit and one 32-bit multiply-add per bin) against the
+    two-sum form that test_oracle.py pins to the FilterBank restatement: random spectra, full-scale
+    spectra (every 30-bit power value at its maximum: the 16-bit output wraps), single bins."""
+    rng = np.random.default_rng(8)
+    top = (1 << 30) - 1
+    cases = [rng.integers(0, 1 << 30, 256) for _ in range(20)] + [rng.integers(0, 5000, 256) for _ in range(5)]
+    cases += [np.full(256, top), np.zeros(256, dtype=np.int64)]
+    for b in (0, 1, 2, 3, 127, 128, 235, 236, 254, 255):
+        e = np.zeros(256, dtype=np.int64)
+        e[b] = top
+        cases.append(e)
+    for pw in cases:
+        assert np.array_equal(LM.mel_lanes_onewide(pw, nf, lo_bit=lo), LM.mel_lanes(pw, nf, lo_bit=lo))
+    # the 16-filter bank has a non-zero rising weight inside segment 0: that form does not apply (two-sum form stays)
+    assert LM.mel_lanes_onewide(cases[0], 16, lo_bit=32) is None
+
+
 def test_log2_table_equals_the_loop():
     t = LM.log2_table()
     for m in list(range(0, 4200)) + list(range(60000, 65536)) + [32767, 32768, 16384, 9999]:
