@@ -44,7 +44,11 @@ constexpr int LR_HALF = LR_NFFT / 2;          // length of the packed complex tr
 constexpr int LR_BINS = LR_HALF + 1;          // 1025 real-spectrum bins
 constexpr int LR_WARPS = 8;                   // frames in flight per CTA
 constexpr int LR_THREADS = 32 * LR_WARPS;
-constexpr int LR_ROW = 33;                    // row pitch of the transposition buffer (float2)
+#ifndef LR_MIRROR
+#define LR_MIRROR 1                           // real-FFT split from registers + mirror-lane shuffles (0: through shared memory)
+#endif
+constexpr int LR_ROW = LR_MIRROR ? 34 : 33;   // row pitch of the transposition buffer (float2); 34: 64-bit row stores and
+                                              // 128-bit column loads are both conflict free
 constexpr int LR_WBUF = 32 * LR_ROW;          // float2 per warp: transposition, spectrum, power
 constexpr int LR_MAX_MELS = 128;
 constexpr int LR_MAX_MFCC = 64;
@@ -243,6 +247,38 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
             if ((j & 7) == 7) __syncwarp();                     // bounds the twiddle loads in flight
         }
         __syncwarp();
+#if LR_MIRROR
+#pragma unroll
+        for (int L = 0; L < 32; L += 2) {                       // lane = k1, values over L, two per 128-bit load
+            const float4 q = *reinterpret_cast<const float4 *>(buf + lane * LR_ROW + L);
+            v[L] = make_float2(q.x, q.y);
+            v[L + 1] = make_float2(q.z, q.w);
+        }
+        __syncwarp();
+        fft32(v);                                               // over L: v[j] = Z[lane + 32 brev5(j)]
+        // real-FFT split: X[k] = F + W^k G, X[1024-k] = conj(F - W^k G), k = lane + 32 k2, k2 < 16.
+        // Z[1024 - k] = Z[(32 - lane) + 32 (31 - k2)] is register 31 - k2 of the mirror lane 32 - lane
+        // (lane 0 mirrors itself one register further round: Z[32 (32 - k2)]), so the partners come
+        // by shuffles and the spectrum never goes back to shared memory.
+        const int src = (32 - lane) & 31;
+        const float2 zc = v[brev5(16)];                         // lane 0: Z[512]
+#pragma unroll
+        for (int k2 = 0; k2 < 16; k2++) {
+            const int k = lane + 32 * k2;
+            float2 sd = v[brev5(31 - k2)];
+            if (lane == 0) sd = v[brev5((32 - k2) & 31)];
+            float2 zb;
+            zb.x = __shfl_sync(0xffffffffu, sd.x, src);
+            zb.y = __shfl_sync(0xffffffffu, sd.y, src);
+            const float2 za = v[brev5(k2)];
+            const float2 F = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
+            const float2 G = make_float2(0.5f * (za.y + zb.y), -0.5f * (za.x - zb.x));
+            const float2 T = cmul(G, tw2[k]);
+            const float pr = F.x + T.x, pi = F.y + T.y, qr = F.x - T.x, qi = F.y - T.y;
+            pw[pa[k]] = pr * pr + pi * pi;                      // bank-padded layout: see the mel walk
+            pw[pa[LR_HALF - k]] = qr * qr + qi * qi;
+        }
+#else
 #pragma unroll
         for (int L = 0; L < 32; L++) v[L] = buf[lane * LR_ROW + L];      // lane = k1, values over L
         __syncwarp();
@@ -272,6 +308,7 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
             pw[pa[k]] = pr * pr + pi * pi;                      // bank-padded layout: see the mel walk
             pw[pa[LR_HALF - k]] = qr * qr + qi * qi;
         }
+#endif
         if (lane == 0) pw[pa[512]] = zc.x * zc.x + zc.y * zc.y;     // W^512 = -i
         __syncwarp();
         if (power_tap) {
