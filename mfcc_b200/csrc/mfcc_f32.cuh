@@ -14,6 +14,10 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#ifndef MFCC_F32_XP_SHFL
+#define MFCC_F32_XP_SHFL 1
+#endif
+
 namespace mfccf {
 
 constexpr int NFFT = 512;
@@ -147,6 +151,34 @@ __device__ __forceinline__ void power_pair_f32(const int16_t *const (&raw)[NP], 
     const int l = lane & 15;
     const float2 *win2 = reinterpret_cast<const float2 *>(tab->window);
     float2 v[NP][16];
+#if MFCC_F32_XP_SHFL
+    // The predecessor of a lane's even sample is the odd sample of the word one lane down (word n - 1
+    // = lane l - 1, same a; for l = 0 lane 15's word of a - 1), so it comes by one shuffle of the
+    // converted value instead of a second load + conversion; lane 15 sends its previous word's.
+    constexpr float BIAS = 12582912.0f + 32768.0f;
+    const int srcl = (lane & 16) | ((l + 15) & 15);
+    float x1prev[NP];
+#pragma unroll
+    for (int f = 0; f < NP; ++f) {
+        // sample before the frame, into lane 15's "previous word" slot (it reaches lane 0 at a = 0)
+        const unsigned up = reinterpret_cast<const unsigned *>(raw[f])[-1] ^ 0x80008000u;
+        x1prev[f] = __uint_as_float(__byte_perm(up, 0x4B400000u, 0x7632)) - BIAS;
+    }
+#pragma unroll
+    for (int a = 0; a < 16; ++a) {
+        const int n = l + 16 * a;
+        const float2 ww = win2[n];
+#pragma unroll
+        for (int f = 0; f < NP; ++f) {
+            const unsigned u = reinterpret_cast<const unsigned *>(raw[f])[n] ^ 0x80008000u;
+            const float x0 = __uint_as_float(__byte_perm(u, 0x4B400000u, 0x7610)) - BIAS;
+            const float x1 = __uint_as_float(__byte_perm(u, 0x4B400000u, 0x7632)) - BIAS;
+            const float xp = __shfl_sync(FULL, l == 15 ? x1prev[f] : x1, srcl);
+            x1prev[f] = x1;
+            v[f][a] = make_float2(fmaf(xp, -0.96875f, x0) * ww.x, fmaf(x0, -0.96875f, x1) * ww.y);
+        }
+    }
+#else
 #pragma unroll
     for (int a = 0; a < 16; ++a) {
         const int n = l + 16 * a;
@@ -157,6 +189,7 @@ __device__ __forceinline__ void power_pair_f32(const int16_t *const (&raw)[NP], 
             v[f][a] = emph_win(r32[n], r32[n - 1], ww.x, ww.y);
         }
     }
+#endif
     // ---- pass 1: DFT-16 over n2, twiddle W256^(n1 k2), transposed store T[k2][n1]
 #pragma unroll
     for (int f = 0; f < NP; ++f) fft16(v[f]);
