@@ -42,6 +42,29 @@ def test_own_arm_lines_carry_the_contract_keys():
             assert c["kind"] in ("reference", "port") and c["cores"] >= 1 and c["value"] > 0 and c["sample"]
 
 
+def test_round2_lines_carry_copy_ceiling_c4_and_baseline_flags():
+    """Round 2: e2e next to its copy-only ceiling at every N, BASELINE configs[3] (C4, strong scaling) at
+    every N, the CPU baseline's build flags and the oracle spot check of the timed launch."""
+    lines = _lines("r02_*_bench_full.json") + _lines("r02_[c-z]_bench_n[248].json")
+    assert len(lines) >= 4
+    for name, d in lines:
+        cc = d["e2e"]["copy_ceiling"]
+        assert cc["unit"] == "frames/s" and cc["value"] > 0
+        assert abs(cc["e2e_over_ceiling"] - d["e2e"]["value"] / cc["value"]) < 1e-9
+        assert cc["e2e_over_ceiling"] >= 0.95, name                 # VERDICT r1: e2e >= 0.95 x the copy-only ceiling
+        c4 = d["c4"]
+        assert c4["scaling"] == "strong" and c4["unit"] == "frames/s" and c4["value"] > 0
+        assert abs(c4["value"] - 16667 * 5645 / (c4["ms_per_pass"] * 1e-3)) < 1e-3 * c4["value"]
+        if d["n_gpus"] == 1:
+            c = d["cpu_baseline"]
+            assert "-O3" in c["build_flags"] and "-march=native" in c["build_flags"]
+            assert c["checker_build"]["value"] > 0
+            if "spot_check" in c:
+                assert c["spot_check"]["bit_exact"] is True
+    ref = _lines("r02_*_bench_reference.json")
+    assert ref and "-march=native" in ref[-1][1]["cpu_baseline"]["build_flags"]
+
+
 def test_reference_arm_line():
     lines = _lines("r01_*_bench_reference.json")
     assert lines
@@ -54,5 +77,5 @@ def test_reference_arm_line():
 def test_bench_cli_surface():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--help"], capture_output=True, text=True)
     assert out.returncode == 0
-    for flag in ("--gpus", "--steps", "--warmup", "--impl"):
+    for flag in ("--gpus", "--steps", "--warmup", "--impl", "--e2e-sweep", "--no-c4"):
         assert flag in out.stdout
