@@ -559,6 +559,11 @@ lr_dct_mma(const float *__restrict__ logmel, const int *__restrict__ clipmax, lo
 #pragma unroll 1
         for (int S = 0; S < 8; ++S) {
             float4 x[4];
+            float part[2][4][4];
+#pragma unroll
+            for (int m = 0; m < 2; ++m)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) part[m][j][0] = part[m][j][1] = part[m][j][2] = part[m][j][3] = 0.0f;
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
                 x[r] = *reinterpret_cast<const float4 *>(rowp[r] + 16 * S);
@@ -581,12 +586,21 @@ lr_dct_mma(const float *__restrict__ logmel, const int *__restrict__ clipmax, lo
                     const float4 b = bfrag[((2 * S + e) * 4 + j) * 32 + lane];
 #pragma unroll
                     for (int m = 0; m < 2; ++m) {
-                        mma_tf32(acc[m][j], ahi[m], b.x, b.y);
-                        mma_tf32(acc[m][j], alo[m], b.x, b.y);
-                        mma_tf32(acc[m][j], ahi[m], b.z, b.w);
+                        // small terms first; the tensor core's own accumulation truncates, so it only ever
+                        // sums the 16 bands of one S step from zero (part), and the running sums are
+                        // ordinary round-to-nearest float32 additions below
+                        mma_tf32(part[m][j], alo[m], b.x, b.y);
+                        mma_tf32(part[m][j], ahi[m], b.z, b.w);
+                        mma_tf32(part[m][j], ahi[m], b.x, b.y);
                     }
                 }
             }
+#pragma unroll
+            for (int m = 0; m < 2; ++m)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[m][j][q] += part[m][j][q];
         }
         // c0, c1: row g, columns 8j + 2t, + 1; c2, c3: row g + 8
 #pragma unroll
