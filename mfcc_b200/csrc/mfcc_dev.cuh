@@ -20,9 +20,6 @@ constexpr int NBINS  = 256;      // FftStream emits bins 0..255, fft_stream.py:2
 constexpr int XW     = 656;      // 32-bit words of the per-warp exchange buffer
 constexpr unsigned FULL = 0xffffffffu;
 
-#ifndef MFCC_CURVE_VEC
-#define MFCC_CURVE_VEC 1
-#endif
 // Tables every CTA copies from global to shared memory once (16-byte multiples).
 struct alignas(16) DevTables {
     int2     twB[128];       // stages 4..7, doubled (2re, 2im): [16 | 16 | 32 | 64] entries
@@ -32,13 +29,9 @@ struct alignas(16) DevTables {
     alignas(16) uint16_t logfrac[2048];  // Log2Fix fraction bits 10..1 for every 12-bit mantissa: see log2fix_tab()
     int2     dct_tw[6 * 32]; // DCT sub-FFT, stage s lane j at [s*32+j], doubled
     int2     dct_twf[32];    // final DCT stage, lane j = bin j, doubled
-#if MFCC_CURVE_VEC
     // window multipliers (9 bits, unsigned), window.py:59-115, as each lane of frame_warp needs them:
     // [q][lane] = the multipliers of positions brev5(lane) + 32 brev4(l), l = 4q..4q+3 (curve_at() for position n)
     uint32_t curveL[4 * 32 * 4];
-#else
-    alignas(16) uint16_t curve[512];     // window multipliers (9 bits, unsigned), window.py:59-115
-#endif
     int16_t  seg_walk[40];   // word address (padded power layout) where lane's walk starts:
                              // segment lane+1, lane 0: segments 0 and 1
     int16_t  seg_close[40];  // closing bin of mel segment g
@@ -136,9 +129,6 @@ __device__ __forceinline__ void bf_pk(int x0r, int x0i, int x1r, int x1i, int w2
 // by -1 so that it runs on the multiplier pipe: the ALU pipe is the busier one in this kernel).
 // Twelve instructions with the two shifts that turn x1 into a multiplicand, against fourteen for
 // the form above; no value is unpacked into a sign-extended integer unless it is multiplied.
-#ifndef MFCC_BF_SFORM
-#define MFCC_BF_SFORM 1
-#endif
 // (S & 0xffff0000) | 0x7fff as ONE lop3 (LUT 0xEA = (a & b) | c).  Written in PTX because the
 // optimiser otherwise turns the OR into an add and moves the constant down the chain, which costs
 // an extra add per component.
@@ -253,7 +243,6 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
     __syncwarp();
     // ---- pass B: lane (h, l4) takes positions 256h + 16m + l4, m = 0..15
     const int h = lane >> 4, l4 = lane & 15;
-#if MFCC_BF_SFORM
     // stage s pairs m, m + 2^(s-4); twiddle index ((m mod 2^(s-4))*16 + l4) * (256 >> s).
     // Indices >= 128 are the stored entry turned by -j: (re, im) -> (im, -re)  (fft.py:55-59)
     unsigned sr[16], si[16];                 // top-half form
@@ -318,70 +307,6 @@ __device__ __forceinline__ void fft512_warp(int (&xr)[16], unsigned *xbuf, const
         im[i] = (int)s0i >> 16;
     }
     __syncwarp();   // xbuf may be reused by the caller
-#else
-#pragma unroll
-    for (int m = 0; m < 16; ++m) {
-        unsigned w = xbuf[xa_addr(16 * h + m, l4)];
-        xr[m] = lo16(w); xi[m] = hi16(w);
-    }
-    __syncwarp();
-    // stage s pairs m, m + 2^(s-4); twiddle index ((m mod 2^(s-4))*16 + l4) * (256 >> s).
-    // Indices >= 128 are the stored entry turned by -j: (re, im) -> (im, -re)  (fft.py:55-59)
-    {   // stage 4: one twiddle per lane
-        const int2 w = tab->twB[l4];
-        const int nwy = -w.y;
-#pragma unroll
-        for (int m = 0; m < 16; m += 2) bf(xr[m], xi[m], xr[m + 1], xi[m + 1], w.x, w.y, nwy);
-    }
-    {   // stage 5
-        const int2 w = tab->twB[16 + l4];
-        const int nwy = -w.y, nwx = -w.x;
-#pragma unroll
-        for (int m = 0; m < 16; m += 4) {
-            bf(xr[m], xi[m], xr[m + 2], xi[m + 2], w.x, w.y, nwy);
-            bf(xr[m + 1], xi[m + 1], xr[m + 3], xi[m + 3], w.y, nwx, w.x);    // W * (-j)
-        }
-    }
-    {   // stage 6
-#pragma unroll
-        for (int mm = 0; mm < 2; ++mm) {
-            const int2 w = tab->twB[32 + mm * 16 + l4];
-            const int nwy = -w.y, nwx = -w.x;
-#pragma unroll
-            for (int m = 0; m < 16; m += 8) {
-                bf(xr[m + mm], xi[m + mm], xr[m + mm + 4], xi[m + mm + 4], w.x, w.y, nwy);
-                bf(xr[m + mm + 2], xi[m + mm + 2], xr[m + mm + 6], xi[m + mm + 6], w.y, nwx, w.x);
-            }
-        }
-    }
-    {   // stage 7, packed into the exchange buffer at natural position + 16*(p >> 8)
-        unsigned *dst = xbuf + 272 * h + l4;
-#pragma unroll
-        for (int mm = 0; mm < 4; ++mm) {
-            const int2 w = tab->twB[64 + mm * 16 + l4];
-            unsigned a0, a1, b0, b1;
-            bf_pk(xr[mm], xi[mm], xr[mm + 8], xi[mm + 8], w.x, w.y, -w.y, a0, a1);
-            bf_pk(xr[mm + 4], xi[mm + 4], xr[mm + 12], xi[mm + 12], w.y, -w.x, w.x, b0, b1);
-            dst[16 * mm] = a0;        dst[16 * (mm + 8)] = a1;
-            dst[16 * (mm + 4)] = b0;  dst[16 * (mm + 12)] = b1;
-        }
-    }
-    __syncwarp();
-    // ---- stage 8: only y0 is ever read (bins 0..255, fft_stream.py:24)
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int b = lane + 32 * i;
-        const int2 w = tab->tw8[b];
-        const unsigned u0 = xbuf[b], u1 = xbuf[272 + b];
-        const int x1r = lo16(u1), x1i = hi16(u1);
-        const int x0r = lo16(u0), x0i = hi16(u0);
-        unsigned qr = (unsigned)(x1r * w.x) - (unsigned)(x1i * w.y) + 16382u;
-        unsigned qi = (unsigned)(x1i * w.x) + (unsigned)(x1r * w.y) + 16382u;
-        re[i] = (int)(((unsigned)x0r << 15) + qr) >> 16;
-        im[i] = (int)(((unsigned)x0i << 15) + qi) >> 16;
-    }
-    __syncwarp();   // xbuf may be reused by the caller
-#endif
 }
 
 // ---------------------------------------------------------------------------------
@@ -534,13 +459,9 @@ __device__ __forceinline__ int dct_warp(unsigned L, const DevTables *tab, int la
         const unsigned x0 = up ? rc : p0;
         const unsigned x1 = up ? p1 : rc;
         const int2 w = tab->dct_tw[s * 32 + j];
-#if MFCC_BF_SFORM
         const Bf o = bf_d(d_of_lo16(x0), d_of_top(x0), lo16(x1), hi16(x1), w.x, w.y, -w.y);
         p0 = __byte_perm(o.s0r, o.s0i, 0x7632);
         p1 = __byte_perm(o.s1r, o.s1i, 0x7632);
-#else
-        bf_pk(lo16(x0), hi16(x0), lo16(x1), hi16(x1), w.x, w.y, p0, p1);
-#endif
     }
     const int2 w = tab->dct_twf[j];
     const unsigned q = (unsigned)(lo16(p0) * w.x) - (unsigned)(hi16(p0) * w.y) + 16382u;

@@ -14,9 +14,6 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
-#ifndef MFCC_F32_XP_SHFL
-#define MFCC_F32_XP_SHFL 1
-#endif
 
 namespace mfccf {
 
@@ -111,20 +108,11 @@ __device__ __forceinline__ void fft16(float2 (&v)[16])
     for (int j = 0; j < 8; ++j) { v[j] = e[j]; v[8 + j] = o[j]; }
 }
 
-// Pre-emphasis + window for the two samples of one 32-bit word (samples 2n, 2n+1).
+// Pre-emphasis + window for the two samples of one 32-bit word (samples 2n, 2n+1), as power_pair_f32 does it.
 // int16 -> float without I2F: with its sign bit flipped a sample is the unsigned number
 // x + 32768; dropped into the low mantissa bits of 1.5 * 2^23 it reads 12582912 + 32768 + x as a
 // float, exactly.  y = x - 0.96875 xp = (32 x - 31 xp) / 32 is exactly representable
 // (|32 x - 31 xp| < 2^22), so the single rounding of the FFMA returns it exactly.
-__device__ __forceinline__ float2 emph_win(unsigned w, unsigned wprev, float w0, float w1)
-{
-    constexpr float BIAS = 12582912.0f + 32768.0f;
-    const unsigned u = w ^ 0x80008000u, up = wprev ^ 0x80008000u;
-    const float x0 = __uint_as_float(__byte_perm(u, 0x4B400000u, 0x7610)) - BIAS;
-    const float x1 = __uint_as_float(__byte_perm(u, 0x4B400000u, 0x7632)) - BIAS;
-    const float xp = __uint_as_float(__byte_perm(up, 0x4B400000u, 0x7632)) - BIAS;
-    return make_float2(fmaf(xp, -0.96875f, x0) * w0, fmaf(x0, -0.96875f, x1) * w1);
-}
 
 // ---------------------------------------------------------------------------------
 // Power spectrum |X[b]|^2 / 512^2, b = 0..256, of TWO frames into shared memory: the lower
@@ -151,7 +139,6 @@ __device__ __forceinline__ void power_pair_f32(const int16_t *const (&raw)[NP], 
     const int l = lane & 15;
     const float2 *win2 = reinterpret_cast<const float2 *>(tab->window);
     float2 v[NP][16];
-#if MFCC_F32_XP_SHFL
     // The predecessor of a lane's even sample is the odd sample of the word one lane down (word n - 1
     // = lane l - 1, same a; for l = 0 lane 15's word of a - 1), so it comes by one shuffle of the
     // converted value instead of a second load + conversion; lane 15 sends its previous word's.
@@ -178,18 +165,6 @@ __device__ __forceinline__ void power_pair_f32(const int16_t *const (&raw)[NP], 
             v[f][a] = make_float2(fmaf(xp, -0.96875f, x0) * ww.x, fmaf(x0, -0.96875f, x1) * ww.y);
         }
     }
-#else
-#pragma unroll
-    for (int a = 0; a < 16; ++a) {
-        const int n = l + 16 * a;
-        const float2 ww = win2[n];
-#pragma unroll
-        for (int f = 0; f < NP; ++f) {
-            const unsigned *r32 = reinterpret_cast<const unsigned *>(raw[f]);
-            v[f][a] = emph_win(r32[n], r32[n - 1], ww.x, ww.y);
-        }
-    }
-#endif
     // ---- pass 1: DFT-16 over n2, twiddle W256^(n1 k2), transposed store T[k2][n1]
 #pragma unroll
     for (int f = 0; f < NP; ++f) fft16(v[f]);

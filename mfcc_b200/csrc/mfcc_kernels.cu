@@ -189,22 +189,16 @@ __device__ __forceinline__ void frame_warp(const int16_t *pre, unsigned *xbuf, c
     const int bt = (int)(__brev((unsigned)lane) >> 27);
     const uint32_t pre_s = smem_u32(pre + bt);
     int xr[16];
-#if MFCC_CURVE_VEC
     unsigned cv[16];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         const uint4 c4 = reinterpret_cast<const uint4 *>(tab->curveL)[q * 32 + lane];
         cv[4 * q] = c4.x; cv[4 * q + 1] = c4.y; cv[4 * q + 2] = c4.z; cv[4 * q + 3] = c4.w;
     }
-#endif
 #pragma unroll
     for (int l = 0; l < 16; ++l) {
         const int n = bt + 32 * brev4(l);
-#if MFCC_CURVE_VEC
         xr[l] = (lds_s16(pre_s + 64u * brev4(l)) * (int)cv[l]) >> 9;
-#else
-        xr[l] = (lds_s16(pre_s + 64u * brev4(l)) * (int)tab->curve[n]) >> 9;
-#endif
         if (TAPS && tp.d_window) tp.d_window[k * NFFT + n] = (int16_t)xr[l];
     }
     int re[8], im[8];
@@ -464,11 +458,7 @@ __global__ void k_frame(const int16_t *y, int16_t *fr, long long n, long long n_
 __global__ void k_window(const int16_t *fr, int16_t *w, long long n_frames, const DevTables *tab) {
     const long long total = n_frames * NFFT;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
-#if MFCC_CURVE_VEC
         w[i] = (int16_t)(((int)fr[i] * (int)tab->curveL[curve_index((int)(i & (NFFT - 1)))]) >> 9);
-#else
-        w[i] = (int16_t)(((int)fr[i] * (int)tab->curve[i & (NFFT - 1)]) >> 9);
-#endif
 }
 
 __global__ void k_power(const int16_t *f, uint32_t *pw, long long n_frames) {
@@ -535,12 +525,8 @@ __global__ void k_frame_v(const int16_t *y, int16_t *fr, long long n, long long 
 
 __global__ void k_window_v(const int16_t *fr, int16_t *w, long long n_frames, const DevTables *tab) {
     __shared__ uint4 curve4[NFFT / 8];
-#if MFCC_CURVE_VEC
     for (int i = threadIdx.x; i < NFFT; i += blockDim.x)
         reinterpret_cast<uint16_t *>(curve4)[i] = (uint16_t)tab->curveL[curve_index(i)];
-#else
-    for (int i = threadIdx.x; i < NFFT / 8; i += blockDim.x) curve4[i] = reinterpret_cast<const uint4 *>(tab->curve)[i];
-#endif
     __syncthreads();
     const long long total = n_frames * (NFFT / 8);
     const uint4 *f4 = reinterpret_cast<const uint4 *>(fr);
@@ -853,11 +839,7 @@ int build_tables(const mfcc_b200_cfg &c, DevTables &t) {
     for (int n = 0; n < NFFT; ++n) {
         if (c.window_curve[n] < 0 || c.window_curve[n] > 511)
             return fail(MFCC_B200_EUNSUPPORTED, "window_curve out of the 9-bit range");
-#if MFCC_CURVE_VEC
         t.curveL[curve_index(n)] = (uint32_t)c.window_curve[n];
-#else
-        t.curve[n] = (uint16_t)c.window_curve[n];
-#endif
     }
     // 32 filters: the one-wide-multiply form of mel_warp() applies when every non-closing weight of
     // segment 0 is zero (see there); otherwise the two-sum form

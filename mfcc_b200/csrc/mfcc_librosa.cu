@@ -44,10 +44,7 @@ constexpr int LR_HALF = LR_NFFT / 2;          // length of the packed complex tr
 constexpr int LR_BINS = LR_HALF + 1;          // 1025 real-spectrum bins
 constexpr int LR_WARPS = 8;                   // frames in flight per CTA
 constexpr int LR_THREADS = 32 * LR_WARPS;
-#ifndef LR_MIRROR
-#define LR_MIRROR 1                           // real-FFT split from registers + mirror-lane shuffles (0: through shared memory)
-#endif
-constexpr int LR_ROW = LR_MIRROR ? 34 : 33;   // row pitch of the transposition buffer (float2); 34: 64-bit row stores and
+constexpr int LR_ROW = 34;                    // row pitch of the transposition buffer (float2): 64-bit row stores and
                                               // 128-bit column loads are both conflict free
 constexpr int LR_WBUF = 32 * LR_ROW;          // float2 per warp: transposition, spectrum, power
 constexpr int LR_MAX_MELS = 128;
@@ -247,7 +244,6 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
             if ((j & 7) == 7) __syncwarp();                     // bounds the twiddle loads in flight
         }
         __syncwarp();
-#if LR_MIRROR
 #pragma unroll
         for (int L = 0; L < 32; L += 2) {                       // lane = k1, values over L, two per 128-bit load
             const float4 q = *reinterpret_cast<const float4 *>(buf + lane * LR_ROW + L);
@@ -278,37 +274,6 @@ lr_logmel(const int16_t *__restrict__ d_x, long long clip_stride, long long n_sa
             pw[pa[k]] = pr * pr + pi * pi;                      // bank-padded layout: see the mel walk
             pw[pa[LR_HALF - k]] = qr * qr + qi * qi;
         }
-#else
-#pragma unroll
-        for (int L = 0; L < 32; L++) v[L] = buf[lane * LR_ROW + L];      // lane = k1, values over L
-        __syncwarp();
-        fft32(v);                                               // over L: v[j] = Z[lane + 32 brev5(j)]
-#pragma unroll
-        for (int j = 0; j < 32; j++) buf[lane + 32 * brev5(j)] = v[j];   // natural order
-        __syncwarp();
-
-        // real-FFT split: X[k] = F + W^k G, X[1024-k] = conj(F - W^k G), k = lane + 32 i < 512.
-        // Both operands are fetched before anything is written: the power goes into the same buffer.
-        float2 zc = buf[512];
-#pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const int k = lane + 32 * i;
-            v[2 * i] = buf[k];
-            v[2 * i + 1] = buf[(LR_HALF - k) & (LR_HALF - 1)];
-        }
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const int k = lane + 32 * i;
-            const float2 za = v[2 * i], zb = v[2 * i + 1];
-            const float2 F = make_float2(0.5f * (za.x + zb.x), 0.5f * (za.y - zb.y));
-            const float2 G = make_float2(0.5f * (za.y + zb.y), -0.5f * (za.x - zb.x));
-            const float2 T = cmul(G, tw2[k]);
-            const float pr = F.x + T.x, pi = F.y + T.y, qr = F.x - T.x, qi = F.y - T.y;
-            pw[pa[k]] = pr * pr + pi * pi;                      // bank-padded layout: see the mel walk
-            pw[pa[LR_HALF - k]] = qr * qr + qi * qi;
-        }
-#endif
         if (lane == 0) pw[pa[512]] = zc.x * zc.x + zc.y * zc.y;     // W^512 = -i
         __syncwarp();
         if (power_tap) {
