@@ -495,6 +495,9 @@ def main():
                           # same step, but the kernel writes the columns straight into pinned host memory
                           ("streaming_hostwrite", lambda: stream_latency(op, dev, 4096, max(1000, args.stream_steps // 2),
                                                                         zero_copy="out")),
+                          # the kernel reads the pinned hops and writes the pinned columns over PCIe itself: one launch
+                          ("streaming_zerocopy", lambda: stream_latency(op, dev, 4096, max(1000, args.stream_steps // 2),
+                                                                       zero_copy=True)),
                           ("streaming_fp32", leg_stream_fp32)):
             try:
                 extras[name] = leg()

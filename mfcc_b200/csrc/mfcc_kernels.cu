@@ -640,8 +640,15 @@ struct StepSmem {
     DevTables tab;
     alignas(16) int16_t pre[WARPS][NFFT];
     alignas(16) unsigned xbuf[WARPS][XW];
+    alignas(16) int16_t st[WARPS][STATE_N];      // the warps' state rows, then their new state rows
+    alignas(16) int16_t hop[WARPS][HOP + 6];     // the warps' hops (row pitch 176: rows stay 16-byte aligned)
 };
 
+// A CTA takes WARPS consecutive streams at a time.  Their state rows (688 bytes each, contiguous) and
+// hops (340 bytes each, contiguous) are staged through shared memory with 128-bit accesses by the
+// whole CTA -- 512-byte requests per warp instead of 64-byte ones -- which matters most when `hop`
+// (or `out`) is pinned HOST memory that the kernel reads over PCIe itself (MFCC.step with host
+// tensors): the step is then one kernel whose PCIe reads overlap its arithmetic.
 template <int NF>
 __global__ void __launch_bounds__(THREADS) mfcc_int_step(int16_t *state, const int16_t *hop, int n_streams,
                                                          int16_t *out, int nceptrums, const DevTables *gtab)
@@ -654,37 +661,83 @@ __global__ void __launch_bounds__(THREADS) mfcc_int_step(int16_t *state, const i
         int4 *dst = reinterpret_cast<int4 *>(&sm->tab);
         for (int i = tid; i < (int)(sizeof(DevTables) / 16); i += THREADS) dst[i] = src[i];
     }
-    __syncthreads();
     const mfcc_b200_taps none = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    for (int s = blockIdx.x * WARPS + warp; s < n_streams; s += gridDim.x * WARPS) {
-        int16_t *st = state + (long long)s * STATE_N;     // st[0] = prev, st[1..342] = history
-        const int16_t *hp = hop + (long long)s * HOP;
-        int16_t *pre = sm->pre[warp];
-        constexpr int HIST = NFFT - HOP;                  // 342
-        // raw(n) for n = -1 .. 511: state then hop
-        int16_t nv[11];                                   // this lane's share of the new state
+    constexpr int HIST = NFFT - HOP;                      // 342
+    constexpr int ST_V = STATE_N / 8;                     // 43 128-bit words per state row
+    const bool st16 = (reinterpret_cast<uintptr_t>(state) & 15) == 0;
+    for (int sb = blockIdx.x * WARPS; sb < n_streams; sb += gridDim.x * WARPS) {
+        const int rows = n_streams - sb < WARPS ? n_streams - sb : WARPS;
+        __syncthreads();                                  // tables are in; the previous block's rows have left
+        // ---- stage the block's state rows and hops
+        {
+            const int16_t *gs = state + (long long)sb * STATE_N;
+            if (st16) {
+                const uint4 *g4 = reinterpret_cast<const uint4 *>(gs);
+                uint4 *s4 = reinterpret_cast<uint4 *>(&sm->st[0][0]);
+                for (int i = tid; i < rows * ST_V; i += THREADS) s4[i] = g4[i];
+            } else {
+                for (int i = tid; i < rows * STATE_N; i += THREADS) (&sm->st[0][0])[i] = gs[i];
+            }
+            const int16_t *gh = hop + (long long)sb * HOP;
+            const int nh = rows * HOP;                    // halfwords, contiguous in global memory
+            if ((reinterpret_cast<uintptr_t>(gh) & 15) == 0) {
+                const uint4 *g4 = reinterpret_cast<const uint4 *>(gh);
+                for (int i = tid; i < nh / 8; i += THREADS) {
+                    const uint4 v = g4[i];
+                    const unsigned w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            const int n = lane + 32 * r;
-            const int cur = n < HIST ? st[1 + n] : hp[n - HIST];
-            const int prv = n <= HIST ? st[n] : hp[n - 1 - HIST];
-            pre[n] = (int16_t)(cur + (prv >> 5) - prv);
+                    for (int q = 0; q < 4; ++q) {         // a 128-bit word may straddle two rows: 32-bit stores (HOP is even)
+                        const int e = 8 * i + 2 * q, r = e / HOP, c = e - r * HOP;
+                        *reinterpret_cast<unsigned *>(&sm->hop[r][c]) = w[q];
+                    }
+                }
+                for (int e = (nh / 8) * 8 + tid; e < nh; e += THREADS) sm->hop[e / HOP][e % HOP] = gh[e];
+            } else {
+                for (int e = tid; e < nh; e += THREADS) sm->hop[e / HOP][e % HOP] = gh[e];
+            }
         }
-        // new state = raw[HOP-1 .. 511]
+        __syncthreads();
+        if (warp < rows) {
+            const int16_t *st = sm->st[warp];             // st[0] = prev, st[1..342] = history
+            const int16_t *hp = sm->hop[warp];
+            int16_t *pre = sm->pre[warp];
+            // raw(n) for n = -1 .. 511: state then hop
+            int16_t nv[11];                               // this lane's share of the new state
 #pragma unroll
-        for (int r = 0; r < 11; ++r) {
-            const int i = lane + 32 * r;                  // 0..342
-            const int n = i + HOP - 1;
-            nv[r] = (i <= HIST) ? (n < HIST ? st[1 + n] : hp[n - HIST]) : (int16_t)0;
-        }
-        __syncwarp();
+            for (int r = 0; r < 16; ++r) {
+                const int n = lane + 32 * r;
+                const int cur = n < HIST ? st[1 + n] : hp[n - HIST];
+                const int prv = n <= HIST ? st[n] : hp[n - 1 - HIST];
+                pre[n] = (int16_t)(cur + (prv >> 5) - prv);
+            }
+            // new state = raw[HOP-1 .. 511]
 #pragma unroll
-        for (int r = 0; r < 11; ++r) {
-            const int i = lane + 32 * r;
-            if (i <= HIST) st[i] = nv[r];
+            for (int r = 0; r < 11; ++r) {
+                const int i = lane + 32 * r;              // 0..342
+                const int n = i + HOP - 1;
+                nv[r] = (i <= HIST) ? (n < HIST ? st[1 + n] : hp[n - HIST]) : (int16_t)0;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int r = 0; r < 11; ++r) {
+                const int i = lane + 32 * r;
+                if (i < STATE_N) sm->st[warp][i] = nv[r];  // element 343 is the row's padding: written as 0
+            }
+            frame_warp<NF, false>(pre, sm->xbuf[warp], &sm->tab, lane, out + (long long)(sb + warp) * nceptrums, nceptrums,
+                                  none, 0);
         }
-        frame_warp<NF, false>(pre, sm->xbuf[warp], &sm->tab, lane, out + (long long)s * nceptrums, nceptrums, none, 0);
-        __syncwarp();
+        __syncthreads();
+        // ---- the new state rows leave
+        {
+            int16_t *gs = state + (long long)sb * STATE_N;
+            if (st16) {
+                uint4 *g4 = reinterpret_cast<uint4 *>(gs);
+                const uint4 *s4 = reinterpret_cast<const uint4 *>(&sm->st[0][0]);
+                for (int i = tid; i < rows * ST_V; i += THREADS) g4[i] = s4[i];
+            } else {
+                for (int i = tid; i < rows * STATE_N; i += THREADS) gs[i] = (&sm->st[0][0])[i];
+            }
+        }
     }
 }
 
