@@ -21,5 +21,6 @@ ncu --set full --import-source on --clock-control none -k regex:lr_logmel -s 3 -
 python profiles/run_librosa.py 300 > $o/${tag}_librosa_rate.txt 2>/dev/null
 python profiles/accuracy.py > $o/${tag}_accuracy.txt 2>/dev/null
 python profiles/stage_rates.py 256 > $o/${tag}_stage_rates.txt 2>/dev/null
-[ -x profiles/micro/mma_bench ] && profiles/micro/mma_bench > $o/${tag}_mma_bench.jsonl
+[ -x profiles/micro/mma_bench ] || nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o profiles/micro/mma_bench profiles/micro/mma_bench.cu
+profiles/micro/mma_bench > $o/${tag}_mma_bench.jsonl
 ls -la $o | tail -12
