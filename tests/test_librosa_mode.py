@@ -51,6 +51,30 @@ def test_restatement_matches_torchaudio(wav):
         assert np.abs(got - ref).max() < 2e-3                  # torchaudio works in float32
 
 
+def test_restatement_matches_the_transformers_port_of_librosa(wav):
+    """A second independent implementation of the same definition: transformers.audio_utils is the
+    numpy port of librosa's mel_filter_bank / stft / power_to_db that the Whisper feature extractor is
+    built on.  Filters to rounding error, mel energies and the clamped dB rows (top_db = 80 under the
+    clip maximum) at its float32 resolution; the ortho DCT-II of those rows is scipy's, which is what
+    librosa.feature.mfcc itself calls."""
+    au = pytest.importorskip("transformers.audio_utils")
+    from scipy.fft import dct
+    mf = au.mel_filter_bank(1025, 128, 0.0, 8000.0, 16000, norm="slaney", mel_scale="slaney")
+    assert np.abs(mf.T - L.mel_filters()).max() < 1e-12
+    rng = np.random.default_rng(5)
+    for x in (wav[:40000], np.clip(rng.normal(0, 3000, 12000), -32768, 32767).astype(np.int16)):
+        y = x.astype(np.float64) / 32768.0
+        kw = dict(frame_length=2048, hop_length=170, fft_length=2048, power=2.0, center=True, pad_mode="reflect",
+                  mel_filters=mf)
+        ref, rt = L.mfcc(x, taps=True)
+        mel = au.spectrogram(y, au.window_function(2048, "hann"), log_mel=None, **kw).T
+        assert mel.shape == rt["mel"].shape and np.abs(mel - rt["mel"]).max() <= 1e-6 * rt["mel"].max()
+        db = au.spectrogram(y, au.window_function(2048, "hann"), log_mel="dB", reference=1.0, min_value=1e-10,
+                            db_range=80.0, **kw).T
+        assert np.abs(db - rt["dbc"]).max() < 1e-4
+        assert np.abs(dct(db.astype(np.float64), type=2, norm="ortho", axis=1)[:, :32] - ref).max() < 1e-3
+
+
 def test_product_tables_match_restatement():
     from mfcc_b200 import tables as T
     assert np.allclose(T.lr_mel_filters(), L.mel_filters(), rtol=0, atol=1e-12)
