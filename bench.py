@@ -28,6 +28,8 @@ N_CLIPS = 10000             # BASELINE.json configs[1]
 NFILT = NCEP = 32
 BYTES_PER_FRAME = 170 * 2 + NCEP * 2    # 340 B read + 64 B written
 SEED0 = 20260000
+WORKLOAD = ("C2: %d synthetic 60 s int16 clips per GPU (960000 samples, 5645 frames each), 512/170 frames, "
+            "32 mel, 32 cepstra, integer (bit-exact) mode")
 
 
 def synth_clips(n_clips, n_samples, device, first_clip=0, out=None):
@@ -169,8 +171,9 @@ def run_reference(args, rank, world):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16",
         "data": "synthetic", "audio_sec_per_sec": v * 170 / 16000,
-        "config": {"workload": "C2: synthetic 60 s int16 clips, 512/170 frames, 32 mel, 32 cepstra, "
-                               "integer mode (bounded sample)", "sample": sample},
+        # the same workload as the GPU arm's line; each timed step is a bounded sample of it
+        "config": {"workload": WORKLOAD % args.clips, "clips_per_gpu": args.clips,
+                   "frames_per_step_per_gpu": args.clips * cfg.num_frames(N_SAMPLES), "sample": sample},
         "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample,
                          "build_flags": "gcc " + RC.FAST_FLAGS, "source": "oracle/mfcc_ref_fast.c"},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -518,9 +521,7 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_max / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16",
             "data": "synthetic", "audio_sec_per_sec": value * 170 / 16000,
-            "config": {"workload": "C2: %d synthetic 60 s int16 clips per GPU (960000 samples, 5645 "
-                                   "frames each), 512/170 frames, 32 mel, 32 cepstra, integer "
-                                   "(bit-exact) mode" % args.clips,
+            "config": {"workload": WORKLOAD % args.clips,
                        "clips_per_gpu": args.clips, "frames_per_step_per_gpu": frames_rank,
                        "l2": "inputs (%.1f GB per step) larger than L2, no flush needed"
                              % (args.clips * N_SAMPLES * 2 / 1e9),
