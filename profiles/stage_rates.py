@@ -49,3 +49,14 @@ for name, fn in (("preemph", op.preemph), ("frame", op.frame), ("window", op.win
 K = cur.shape[0]
 _, ms = timed(op, x)
 print("fused        %10.3f  (%d frames, %.4g frames/s; the whole chain in one launch)" % (ms, K, K / ms * 1e3))
+# context for the write-heavy stages: what this GPU does for a pure write, a 1:1 copy and a 1:3 expansion
+# (Frame reads every sample once from HBM and writes it three times)
+buf = torch.empty(1_536_000_000 // 2, dtype=torch.int16, device=dev)
+src = torch.empty(512_000_000 // 2, dtype=torch.int16, device=dev)
+_, ms = timed(lambda t: t.zero_(), buf)
+print("memset       %10.3f %10.3f %10.1f   (pure write)" % (ms, nbytes(buf) / 1e9, nbytes(buf) / 1e9 / ms * 1e3))
+_, ms = timed(lambda t: buf[:t.numel()].copy_(t), src)
+print("copy 1:1     %10.3f %10.3f %10.1f   (read + write)" % (ms, 2 * nbytes(src) / 1e9, 2 * nbytes(src) / 1e9 / ms * 1e3))
+_, ms = timed(lambda t: buf.view(3, -1).copy_(t.expand(3, -1)), src)
+print("expand 1:3   %10.3f %10.3f %10.1f   (one read, three writes: Frame's traffic shape)" % (
+    ms, (nbytes(src) + nbytes(buf)) / 1e9, (nbytes(src) + nbytes(buf)) / 1e9 / ms * 1e3))
